@@ -1,0 +1,187 @@
+/* stereo_geom.h - C ABI of libstereo_geom.so, the B200 (sm_100a) geometry library for the
+ * per-frame path that wraps every network of StereoAlgorithms:
+ *
+ *     rectify -> preprocess -> [network, untouched] -> reproject (point cloud) -> heatmap
+ *
+ * Plain C: opaque handle, raw pointers, sizes and pitches.  No OpenCV, TensorRT or torch types.
+ * Every function returns SA_OK (0) or a negative sa_status; nothing asserts or prints.  The
+ * message for the last failure on a handle is sa_last_error(h).  There is no CPU fallback: if no
+ * CUDA device is usable, sa_create fails with SA_ERR_CUDA.
+ *
+ * Each declaration cites the reference interface it replaces (paths relative to the reference
+ * tree).  The reference-named entry points (Initialize / Run<Model>[_RectifyImage] / Version /
+ * Release) are in stereo_algorithms_compat.h, built on top of this header.
+ *
+ * Layouts (N = number of stereo pairs in the call, W x H = camera image, w x h = network size,
+ * equal to W x H unless sa_config.net_width/net_height say otherwise):
+ *   raw / rectified image   uint8  [N][H][W][3]   BGR, rows `pitch` bytes apart on input
+ *   network tensor          f32|f16 [N][3][h][w]  RGB planes, one tensor per eye
+ *                           (HitNet: a single [N][6][h][w] tensor, L_r L_g L_b R_r R_g R_b)
+ *   disparity               float  [N][planes][h][w]  planes = 2 for CREStereo (plane 0 is used), else 1
+ *   point cloud, dense      float  [N][h*w][6]    x y z r g b, row-major pixels, nothing filtered
+ *   point cloud, compact    float  [N][h*w][6]    first counts[i] rows of frame i are valid
+ *   heatmap                 uint8  [N][h][w][3]   BGR (JET)
+ */
+#ifndef STEREO_GEOM_H_
+#define STEREO_GEOM_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SA_API __attribute__((visibility("default")))
+
+typedef struct sa_handle sa_handle;
+typedef void* sa_stream; /* a cudaStream_t, or NULL for the handle's own stream */
+
+enum sa_status {
+    SA_OK = 0,
+    SA_ERR_INVALID_ARG = -1,
+    SA_ERR_NOT_READY = -2, /* calibration / maps / disparity missing for the requested stage */
+    SA_ERR_CUDA = -3,
+    SA_ERR_IO = -4,
+    SA_ERR_PARSE = -5,
+    SA_ERR_TOO_LARGE = -6, /* n > max_batch, or a size beyond a documented limit */
+    SA_ERR_NOMEM = -7
+};
+
+/* Which network the tensors are prepared for.  Selects the normalisation of the preprocess
+ * stage and the disparity convention of the reproject stage:
+ *   RAFTSTEREO       f32(c), no scaling          RAFTStereo/src/stereo_preprocess.cu:4-39; reproject negates the
+ *                                                disparity and writes it back (:54-55)
+ *   HITNET           f32(f64(c)/255.0), 6-ch     HitNet/src/HitNet_preprocess.cu:4-53
+ *   CRESTEREO        f32(c), no scaling          CREStereo/src/CREStereo_preprocess.cu:4-39; disparity = plane 0 of 2
+ *                                                (CREStereo/src/TRTCREStereo.cpp:15,133)
+ *   FASTACVNET_PLUS  (c/255.0f - mean)/std with double literals   FastACVNet_plus/src/FastACVNet_plus_preprocess.cu:27-29 */
+enum sa_model { SA_MODEL_RAFTSTEREO = 0, SA_MODEL_HITNET = 1, SA_MODEL_CRESTEREO = 2, SA_MODEL_FASTACVNET_PLUS = 3 };
+enum sa_dtype { SA_F32 = 0, SA_F16 = 1 };
+enum sa_where { SA_HOST = 0, SA_DEVICE = 1 };
+enum sa_eye { SA_LEFT = 0, SA_RIGHT = 1 };
+enum sa_reproject_mode { SA_DENSE = 0, SA_COMPACT = 1 };
+enum sa_stage { SA_STAGE_RECTIFY = 0, SA_STAGE_RESIZE = 1, SA_STAGE_REPROJECT = 2, SA_STAGE_HEATMAP = 3, SA_STAGE_STUB = 4,
+                SA_STAGE_MAPS = 5, SA_STAGE_COUNT_ = 6 };
+
+enum sa_flags {
+    SA_FLAG_TIMING = 1u << 0,      /* record CUDA events around every stage (sa_stage_time) */
+    SA_FLAG_NO_HEATMAP_BUF = 1u << 1, /* do not allocate the internal heatmap buffer */
+    SA_FLAG_NO_POINT_BUF = 1u << 2    /* do not allocate the internal point-cloud buffer (caller passes device `out`) */
+};
+
+/* Replaces the constants the reference hard-codes (INPUT_H/INPUT_W/batch 1,
+ * FastACVNet_plus/src/TRTFastACVNet_plus.cpp:13-18, FastACVNet_plus/include/TRTFastACVNet_plus.h:15). */
+typedef struct sa_config {
+    int struct_size; /* = sizeof(sa_config) */
+    int gpu_id;      /* cudaSetDevice(gpu_id), TRTFastACVNet_plus.cpp:45 - re-applied on every call */
+    int width, height;         /* camera image size */
+    int net_width, net_height; /* network input size; 0 = same as the image (the reference asserts equality, :121-122) */
+    int model;                 /* enum sa_model */
+    int tensor_dtype;          /* enum sa_dtype (the reference is f32 only) */
+    int max_batch;             /* buffers are sized for this many stereo pairs (the reference: 1) */
+    unsigned flags;            /* enum sa_flags */
+} sa_config;
+
+/* Buffer allocation of FastACVNet_plus::Initialize (TRTFastACVNet_plus.cpp:91-115) without the TensorRT part. */
+SA_API int sa_create(const sa_config* cfg, sa_handle** out);
+/* FastACVNet_plus::Release (TRTFastACVNet_plus.cpp:171-192); unlike the reference the handle itself is freed too. */
+SA_API int sa_destroy(sa_handle* h);
+SA_API const char* sa_version(void);
+/* Replaces CUDA_CHECK's stderr + assert(0) (FastACVNet_plus/include/TRTFastACVNet_plus.h:18-26).  h may be NULL
+ * (message of the last failed sa_create on this thread). */
+SA_API const char* sa_last_error(const sa_handle* h);
+
+/* ReadObjectYml (FastACVNet_plus/src/FastACVNet_plus_Algorithm.cpp:98-114): the 11 !!opencv-matrix nodes of a
+ * StereoCalibration.yml.  Also computes the rectification maps for both eyes on the device - once, not per frame
+ * as the reference does (:139-140). */
+SA_API int sa_load_calibration_yaml(sa_handle* h, const char* path);
+/* Same, from memory (struct CalibrationParam, FastACVNet_plus/include/TRTFastACVNet_plus.h:30-43).  Row-major
+ * doubles: K 3x3, D nD (4,5,8,12 or 14) coefficients, R 3x3, P 3x4, Q 4x4. */
+SA_API int sa_set_calibration(sa_handle* h, const double* K_l, const double* D_l, int nD_l, const double* R_L, const double* P1,
+                              const double* K_r, const double* D_r, int nD_r, const double* R_R, const double* P2, const double* Q);
+/* Calibrationparam_Q[i] = (float)Q[i] (TRTFastACVNet_plus.cpp:107-113); use after a resize changed the geometry. */
+SA_API int sa_set_Q(sa_handle* h, const double* Q16);
+SA_API int sa_get_Q(sa_handle* h, double* Q16);
+/* Maps in cv::initUndistortRectifyMap's CV_16SC2 + CV_16UC1 layout (host pointers): map1 int16 [H][W][2] = (x,y),
+ * map2 uint16 [H][W] = (fy<<5)|fx.  sa_set_maps injects caller-computed maps instead of the library's. */
+SA_API int sa_set_maps(sa_handle* h, int eye, const int16_t* map1, const uint16_t* map2);
+SA_API int sa_get_maps(sa_handle* h, int eye, int16_t* map1, uint16_t* map2);
+
+/* Stage A.  RectifyImage (FastACVNet_plus_Algorithm.cpp:132-145: 2x remap INTER_LINEAR, bit-exact) fused with
+ * <Model>_preprocess (TRTFastACVNet_plus.cpp:130-134) for n pairs in one launch.  left/right: [n][H] rows of `pitch`
+ * bytes (0 = 3*W), host or device.  rectify = 0 is the reference's plain Run<Model> (images already rectified).
+ * Results stay on the device: sa_input_tensor, sa_copy_rectified. */
+SA_API int sa_rectify_preprocess(sa_handle* h, int n, const uint8_t* left, const uint8_t* right, size_t pitch, int where,
+                                 int rectify, sa_stream stream);
+/* buffers[inputIndex1/2] and buffers[outputIndex] of the reference (TRTFastACVNet_plus.cpp:93-95): the device
+ * pointers a TensorRT context is bound to.  HitNet: one 6-channel tensor, `eye` is ignored. */
+SA_API void* sa_input_tensor(sa_handle* h, int eye);
+SA_API float* sa_disparity_buffer(sa_handle* h);
+SA_API int sa_disparity_planes(const sa_handle* h);
+/* Stand-in for context->enqueueV3(stream) (TRTFastACVNet_plus.cpp:152) when no engine is available: fills the
+ * disparity buffer with a smooth synthetic field, ~5 % zeros and ~1 % negatives (RAFTStereo: sign-flipped, as
+ * that network emits it). */
+SA_API int sa_stub_disparity(sa_handle* h, int n, unsigned seed, sa_stream stream);
+/* Upload a network output [n][planes][h][w] (tests, or an engine that ran elsewhere). */
+SA_API int sa_set_disparity(sa_handle* h, int n, const float* disparity, int where, sa_stream stream);
+
+/* Stage B.  <Model>_reprojectImageTo3D (FastACVNet_plus/src/FastACVNet_plus_preprocess.cu:41-63,75-80) for n frames.
+ * mode SA_DENSE: every pixel, like the reference.  SA_COMPACT (extension): only pixels with a finite disparity
+ * > 0, order preserved, counts[i] rows valid in frame i's slot.  out: NULL (keep in the internal buffer),
+ * a device buffer (written directly) or a host buffer (copied; the call then synchronises).  counts: host or device
+ * like `out`, may be NULL for SA_DENSE. */
+SA_API int sa_reproject(sa_handle* h, int n, int mode, float* out, int* counts, int where, sa_stream stream);
+SA_API float* sa_pointcloud_buffer(sa_handle* h);
+
+/* Stage C.  heatmap() of the demo (FastACVNet_plus/test/main.cpp:7-24), per frame, on the disparity as returned
+ * (after RAFTStereo's sign flip).  out as for sa_reproject. */
+SA_API int sa_heatmap(sa_handle* h, int n, uint8_t* out, int where, sa_stream stream);
+
+/* Read-backs (the cudaMemcpy D2H + clone of TRTFastACVNet_plus.cpp:163-168; rectified images are what the
+ * reference leaves in the caller's cv::Mat). */
+SA_API int sa_copy_rectified(sa_handle* h, int n, int eye, uint8_t* out, int where, sa_stream stream);
+SA_API int sa_copy_net_image(sa_handle* h, int n, int eye, uint8_t* out, int where, sa_stream stream); /* resized u8, if resizing */
+SA_API int sa_copy_tensor(sa_handle* h, int n, int eye, void* out, int where, sa_stream stream);
+SA_API int sa_copy_disparity(sa_handle* h, int n, float* out, int where, sa_stream stream); /* plane 0 -> [n][h][w] */
+SA_API int sa_synchronize(sa_handle* h);
+
+/* The reference's whole Run<Model>[_RectifyImage] data flow for n pairs with HOST buffers (TRTFastACVNet_plus.cpp:
+ * 119-170): upload, stage A, network slot, stage B, download - pipelined in chunks over copy/compute streams.
+ * Any output pointer may be NULL to skip that download.  The network slot runs the engine callback if one is set,
+ * else the synthetic stub when stub_seed != 0, else uses the disparity buffer as it is. */
+typedef int (*sa_engine_fn)(void* user, sa_stream stream, int first_frame, int n, const void* left_tensor,
+                            const void* right_tensor, float* disparity);
+SA_API int sa_set_engine(sa_handle* h, sa_engine_fn fn, void* user);
+SA_API int sa_run_batch(sa_handle* h, int n, const uint8_t* left, const uint8_t* right, int rectify, unsigned stub_seed,
+                        float* pointcloud, float* disparity, uint8_t* rect_left, uint8_t* rect_right, uint8_t* heatmap);
+
+/* Host-only helpers: usable without a CUDA device.
+ * sa_parse_calibration_yaml is the file-reading half of ReadObjectYml (FastACVNet_plus_Algorithm.cpp:98-114): all 11
+ * matrices of struct CalibrationParam (TRTFastACVNet_plus.h:30-43), row-major.  err (optional) receives the message.
+ * sa_norm_lut gives the 3x256 normalisation table (R,G,B planes) that stage A applies for `model`; sa_resize_table the
+ * source index / weight table (s0 s1 c0 c1, each [dst]) of one axis of the 8-bit INTER_LINEAR resize. */
+typedef struct sa_calibration {
+    double K_l[9], D_l[14], R_L[9], P1[12];
+    double K_r[9], D_r[14], R_R[9], P2[12];
+    double Q[16], R[9], T[3];
+    int nD_l, nD_r;
+} sa_calibration;
+SA_API int sa_parse_calibration_yaml(const char* path, sa_calibration* out, char* err, size_t err_len);
+SA_API int sa_norm_lut(int model, float* lut768);
+SA_API int sa_resize_table(int dst, int src, int* table);
+
+/* Pinned host memory for the buffers above (cudaMallocHost of TRTFastACVNet_plus.cpp:98-99). */
+SA_API int sa_host_alloc(void** p, size_t bytes);
+SA_API int sa_host_free(void* p);
+
+/* Observability (the reference only prints a wall-clock "inference time", TRTFastACVNet_plus.cpp:165-166). */
+SA_API int sa_stage_time(sa_handle* h, int stage, double* total_ms, long* launches); /* needs SA_FLAG_TIMING; synchronises */
+SA_API int sa_reset_timing(sa_handle* h);
+SA_API long sa_launch_count(const sa_handle* h); /* kernels launched by this handle so far */
+SA_API int sa_set_option(sa_handle* h, const char* key, long value); /* tuning knobs, see DESIGN.md */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* STEREO_GEOM_H_ */

@@ -1,0 +1,194 @@
+// Internal declarations shared by the translation units of libstereo_geom.so.
+#pragma once
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <string>
+#include <vector>
+
+#include "../../include/stereo_geom.h"
+
+namespace sa {
+
+// ---- tiling of the fused rectify kernel -----------------------------------------------------
+constexpr int kTileW = 64;          // output pixels per tile row (one warp covers 32 of them)
+constexpr int kTileH = 16;          // output rows per tile
+constexpr int kRectThreads = 256;   // 4 output pixels per thread
+constexpr int kFootprintWords = 3072;  // staged source pixels per tile (BGRx words, 12 KB)
+
+// Bounding box, in source-image pixels, of all bilinear taps of one output tile.  Coordinates are
+// "extended": they may reach 2 pixels outside the image, where the staging writes zeros
+// (BORDER_CONSTANT 0).  w == 0 marks a tile whose footprint does not fit kFootprintWords: it is
+// gathered directly from global memory.
+struct TileInfo {
+    short x0, y0;  // top-left (x0 is a multiple of 4)
+    short w, h;    // extent (w is a multiple of 4)
+};
+
+struct MapParams {
+    double iR[9];
+    double k[12];  // k1 k2 p1 p2 k3 k4 k5 k6 s1 s2 s3 s4
+    double fx, fy, cx, cy;
+};
+
+struct StageTimer {
+    std::vector<cudaEvent_t> begin[SA_STAGE_COUNT_], end[SA_STAGE_COUNT_];
+    size_t used[SA_STAGE_COUNT_] = {0};
+};
+
+}  // namespace sa
+
+struct sa_handle {
+    sa_config cfg{};
+    int W = 0, H = 0, w = 0, h = 0;  // image / network size
+    bool resize = false;
+    int planes = 1;
+    int max_n = 0;
+    size_t tensor_elt = 4;
+
+    cudaStream_t stream = nullptr, s_h2d = nullptr, s_d2h = nullptr;
+    std::vector<cudaEvent_t> ev_pool;
+
+    // calibration
+    bool have_calib = false, have_q = false;
+    bool have_maps[2] = {false, false};
+    double K[2][9]{}, D[2][14]{}, R[2][9]{}, P[2][12]{}, Q[16]{};
+    int nD[2] = {0, 0};
+    float Qf[16]{};
+
+    // device buffers
+    uint8_t* raw[2] = {nullptr, nullptr};     // uploaded camera frames   [N][H][W][3]
+    uint8_t* rect[2] = {nullptr, nullptr};    // rectified frames         [N][H][W][3]
+    uint8_t* net_u8[2] = {nullptr, nullptr};  // resized frames (resize only) [N][h][w][3]
+    void* tensor[2] = {nullptr, nullptr};     // network inputs; HitNet: tensor[1] = tensor[0] + 3 planes
+    float* disp = nullptr;                    // [N][planes][h][w]
+    float* points = nullptr;                  // [N][h*w][6]
+    uint8_t* heat = nullptr;                  // [N][h][w][3]
+    int* counts = nullptr;                    // [N]
+    int* map1[2] = {nullptr, nullptr};        // (x | y << 16) int16 pairs, [H][W]
+    uint16_t* map2[2] = {nullptr, nullptr};
+    sa::TileInfo* tiles[2] = {nullptr, nullptr};
+    float* lut32 = nullptr;                   // [3][256]
+    __half* lut16 = nullptr;
+    unsigned* minmax = nullptr;               // [N][2] ordered-uint encodings (min, ~max)
+    int* blk_counts = nullptr;                // [N][blocks per frame]  (compaction scratch)
+    int* blk_offsets = nullptr;
+    int* rs_x = nullptr;                      // resize tables: x0 x1 a0 a1 [w], y0 y1 b0 b1 [h]
+    int* rs_y = nullptr;
+
+    // state
+    const uint8_t* color_src[2] = {nullptr, nullptr};  // what reproject takes colours from / copy_rectified returns
+    size_t color_pitch = 0, color_frame = 0;
+    int minmax_valid = 0;  // number of frames whose min/max is current
+    int n_last = 0;
+    sa_engine_fn engine = nullptr;
+    void* engine_user = nullptr;
+
+    // options
+    long opt_frame_fastest = 1;
+    long opt_chunk = 8;
+    long opt_force_direct = 0;
+
+    long launches = 0;
+    sa::StageTimer timer;
+    std::string err;
+};
+
+namespace sa {
+
+int fail(sa_handle* h, int code, const char* fmt, ...);
+void set_global_error(const char* msg);
+
+#define SA_CUDA(h, expr)                                                                               \
+    do {                                                                                               \
+        cudaError_t e_ = (expr);                                                                       \
+        if (e_ != cudaSuccess) return sa::fail((h), SA_ERR_CUDA, "%s: %s (%s:%d)", #expr, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+struct StageScope {  // records timing events around a stage when SA_FLAG_TIMING is set
+    sa_handle* h;
+    int stage;
+    cudaStream_t s;
+    StageScope(sa_handle* h, int stage, cudaStream_t s);
+    ~StageScope();
+};
+
+// calib_yaml.cpp
+struct YamlMat {
+    std::string name;
+    int rows = 0, cols = 0;
+    std::vector<double> data;
+};
+int parse_opencv_yaml(const char* path, std::vector<YamlMat>& out, std::string& err);
+
+// kernels (each returns a cudaError_t from the launch)
+cudaError_t launch_init_maps(const MapParams& p, int W, int H, int* map1, uint16_t* map2, cudaStream_t s);
+cudaError_t launch_tile_info(const int* map1, int W, int H, TileInfo* tiles, int tiles_x, int tiles_y, int force_direct, cudaStream_t s);
+
+struct RectifyArgs {
+    const uint8_t* src[2];
+    uint8_t* rect[2];
+    void* tensor[2];
+    const int* map1[2];
+    const uint16_t* map2[2];
+    const TileInfo* tiles[2];
+    const void* lut;          // float[3][256] or __half[3][256]
+    size_t src_pitch, src_frame;       // bytes
+    size_t tensor_frame;               // elements between consecutive frames of one eye
+    int W, H, n;
+    int model, dtype;
+    int write_tensor;                  // 0 when a resize follows
+    int frame_fastest;
+};
+cudaError_t launch_rectify(const RectifyArgs& a, cudaStream_t s, long* launches);
+
+struct PreprocArgs {  // rectify = 0 path, and the second half of the resize path
+    const uint8_t* src[2];
+    void* tensor[2];
+    const void* lut;
+    size_t src_pitch, src_frame, tensor_frame;
+    int W, H, n, model, dtype;
+};
+cudaError_t launch_preprocess(const PreprocArgs& a, cudaStream_t s, long* launches);
+
+struct ResizeArgs {
+    const uint8_t* src[2];   // rectified [n][H][W][3]
+    uint8_t* dst[2];         // [n][h][w][3]
+    const int* tab_x;        // x0 x1 a0 a1, each [w]
+    const int* tab_y;        // y0 y1 b0 b1, each [h]
+    size_t src_pitch, src_frame;
+    int W, H, w, h, n, area2x;
+};
+cudaError_t launch_resize(const ResizeArgs& a, cudaStream_t s, long* launches);
+
+struct ReprojectArgs {
+    float* disp;              // frame f at disp + f*disp_frame (plane 0)
+    size_t disp_frame;        // floats
+    const uint8_t* color;     // BGR
+    size_t color_pitch, color_frame;
+    float* points;            // frame f at points + f*w*h*6
+    float q[16];
+    int w, h, n;
+    int negate;               // RAFTStereo
+    int compact;
+    unsigned* minmax;         // [n][2], may be null
+    int* blk_counts;          // scratch [n][nblk]
+    int* blk_offsets;         // scratch [n][nblk]
+    int* counts;              // [n] device
+};
+cudaError_t launch_reproject(const ReprojectArgs& a, cudaStream_t s, long* launches);
+int reproject_blocks_per_frame(int w, int h);
+
+cudaError_t launch_minmax(const float* disp, size_t disp_frame, int npix, int n, unsigned* minmax, cudaStream_t s, long* launches);
+cudaError_t launch_heatmap(const float* disp, size_t disp_frame, int npix, int n, const unsigned* minmax, uint8_t* out, cudaStream_t s, long* launches);
+cudaError_t launch_stub(float* disp, size_t disp_frame, int planes, int w, int h, int first_frame, int n, unsigned seed, int negate,
+                        cudaStream_t s, long* launches);
+cudaError_t launch_copy_plane0(const float* disp, size_t disp_frame, size_t npix, int n, float* out, cudaStream_t s, long* launches);
+
+void build_norm_lut(int model, float* lut /*[3][256]*/);
+void build_resize_table(int D, int S, int* s0, int* s1, int* c0, int* c1);
+
+}  // namespace sa

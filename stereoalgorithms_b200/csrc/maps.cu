@@ -1,0 +1,106 @@
+// Rectification maps on the device, once per calibration (the reference recomputes them on the CPU
+// for every frame: FastACVNet_plus/src/FastACVNet_plus_Algorithm.cpp:139-140), plus the per-tile
+// source footprint table the fused rectify kernel stages from.
+//
+// init_maps_kernel reproduces cv::initUndistortRectifyMap(K, D, R, P, size, CV_16SC2) bit for bit:
+// float64 throughout, every product and sum rounded separately (no FMA contraction - hence the
+// explicit __dmul_rn/__dadd_rn), the same operation order as OpenCV's per-pixel loop, cvRound's
+// x86 behaviour for values that do not fit an int (INT_MIN), saturating int16 packing.
+#include "common.h"
+
+namespace sa {
+
+__device__ __forceinline__ double mul(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ double add(double a, double b) { return __dadd_rn(a, b); }
+__device__ __forceinline__ double dvd(double a, double b) { return __ddiv_rn(a, b); }
+
+__device__ __forceinline__ int cv_round_i32(double v)
+{
+    double r = rint(v);  // round half to even
+    if (!(r >= -2147483648.0 && r <= 2147483647.0)) return INT_MIN;
+    return (int)r;
+}
+
+__global__ void __launch_bounds__(256) init_maps_kernel(MapParams p, int W, int H, int* __restrict__ map1, uint16_t* __restrict__ map2)
+{
+    int j = blockIdx.x * blockDim.x + threadIdx.x;
+    int i = blockIdx.y;
+    if (j >= W || i >= H) return;
+    const double dj = (double)j, di = (double)i;
+    double X = add(add(mul(p.iR[0], dj), mul(p.iR[1], di)), p.iR[2]);
+    double Y = add(add(mul(p.iR[3], dj), mul(p.iR[4], di)), p.iR[5]);
+    double Wd = add(add(mul(p.iR[6], dj), mul(p.iR[7], di)), p.iR[8]);
+    double w = dvd(1.0, Wd), x = mul(X, w), y = mul(Y, w);
+    double x2 = mul(x, x), y2 = mul(y, y), r2 = add(x2, y2), _2xy = mul(mul(2.0, x), y);
+    const double k1 = p.k[0], k2 = p.k[1], p1 = p.k[2], p2 = p.k[3], k3 = p.k[4], k4 = p.k[5], k5 = p.k[6], k6 = p.k[7];
+    const double s1 = p.k[8], s2 = p.k[9], s3 = p.k[10], s4 = p.k[11];
+    double num = add(1.0, mul(add(mul(add(mul(k3, r2), k2), r2), k1), r2));
+    double den = add(1.0, mul(add(mul(add(mul(k6, r2), k5), r2), k4), r2));
+    double kr = dvd(num, den);
+    double xd = add(add(add(add(mul(x, kr), mul(p1, _2xy)), mul(p2, add(r2, mul(2.0, x2)))), mul(s1, r2)), mul(mul(s2, r2), r2));
+    double yd = add(add(add(add(mul(y, kr), mul(p1, add(r2, mul(2.0, y2)))), mul(p2, _2xy)), mul(s3, r2)), mul(mul(s4, r2), r2));
+    double u = add(mul(p.fx, xd), p.cx), v = add(mul(p.fy, yd), p.cy);
+    int iu = cv_round_i32(mul(u, 32.0)), iv = cv_round_i32(mul(v, 32.0));
+    int sx = max(-32768, min(32767, iu >> 5)), sy = max(-32768, min(32767, iv >> 5));
+    size_t o = (size_t)i * W + j;
+    map1[o] = (sx & 0xffff) | (sy << 16);
+    map2[o] = (uint16_t)(((iv & 31) << 5) | (iu & 31));
+}
+
+cudaError_t launch_init_maps(const MapParams& p, int W, int H, int* map1, uint16_t* map2, cudaStream_t s)
+{
+    dim3 grid((W + 255) / 256, H);
+    init_maps_kernel<<<grid, 256, 0, s>>>(p, W, H, map1, map2);
+    return cudaGetLastError();
+}
+
+// One CTA per output tile: min/max of the (clamped) integer source coordinates of its pixels.
+__global__ void __launch_bounds__(256) tile_info_kernel(const int* __restrict__ map1, int W, int H, TileInfo* __restrict__ tiles, int tiles_x,
+                                                        int force_direct)
+{
+    const int tile = blockIdx.x;
+    const int tx0 = (tile % tiles_x) * kTileW, ty0 = (tile / tiles_x) * kTileH;
+    int xmin = 1 << 20, xmax = -(1 << 20), ymin = 1 << 20, ymax = -(1 << 20);
+    for (int k = threadIdx.x; k < kTileW * kTileH; k += blockDim.x) {
+        int x = tx0 + (k % kTileW), y = ty0 + (k / kTileW);
+        if (x < W && y < H) {
+            int m = map1[(size_t)y * W + x];
+            int sx = (int)(short)(m & 0xffff), sy = m >> 16;
+            sx = max(-2, min(W, sx));
+            sy = max(-2, min(H, sy));
+            xmin = min(xmin, sx); xmax = max(xmax, sx);
+            ymin = min(ymin, sy); ymax = max(ymax, sy);
+        }
+    }
+    __shared__ int red[4][8];
+    for (int o = 16; o; o >>= 1) {
+        xmin = min(xmin, __shfl_xor_sync(0xffffffffu, xmin, o));
+        xmax = max(xmax, __shfl_xor_sync(0xffffffffu, xmax, o));
+        ymin = min(ymin, __shfl_xor_sync(0xffffffffu, ymin, o));
+        ymax = max(ymax, __shfl_xor_sync(0xffffffffu, ymax, o));
+    }
+    int warp = threadIdx.x >> 5;
+    if ((threadIdx.x & 31) == 0) { red[0][warp] = xmin; red[1][warp] = xmax; red[2][warp] = ymin; red[3][warp] = ymax; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int k = 1; k < 8; k++) {
+            xmin = min(xmin, red[0][k]); xmax = max(xmax, red[1][k]);
+            ymin = min(ymin, red[2][k]); ymax = max(ymax, red[3][k]);
+        }
+        TileInfo t;
+        int x0 = xmin & ~3;                      // floor to a multiple of 4 (also for negatives)
+        int w = ((xmax + 2 - x0) + 3) & ~3;      // taps reach sx+1
+        int h = ymax + 2 - ymin;
+        t.x0 = (short)x0; t.y0 = (short)ymin; t.w = (short)w; t.h = (short)h;
+        if (force_direct || w * h > kFootprintWords || w <= 0 || h <= 0) { t.w = 0; t.h = 0; }
+        tiles[tile] = t;
+    }
+}
+
+cudaError_t launch_tile_info(const int* map1, int W, int H, TileInfo* tiles, int tiles_x, int tiles_y, int force_direct, cudaStream_t s)
+{
+    tile_info_kernel<<<tiles_x * tiles_y, 256, 0, s>>>(map1, W, H, tiles, tiles_x, force_direct);
+    return cudaGetLastError();
+}
+
+}  // namespace sa

@@ -1,0 +1,211 @@
+// Stage C (heatmap) and the small kernels around the network slot: per-frame disparity min/max, JET heatmap,
+// synthetic-disparity stub, plane-0 extraction, and the u8 INTER_LINEAR resize of the optional resize path.
+#include <cfloat>
+
+#include "common.h"
+
+namespace sa {
+
+namespace {
+
+__constant__ uint32_t c_jet[256] = {
+#include "jet_lut.inc"
+};
+
+__device__ __forceinline__ unsigned enc_ordered(float f)
+{
+    unsigned b = __float_as_uint(f);
+    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__device__ __forceinline__ float dec_ordered(unsigned e)
+{
+    return __uint_as_float((e & 0x80000000u) ? (e & 0x7fffffffu) : ~e);
+}
+
+// ---- min/max (standalone; normally fused into the reproject kernels) ---------------------------------------
+__global__ void __launch_bounds__(256) minmax_kernel(const float* __restrict__ disp, size_t disp_frame, int npix, unsigned* __restrict__ minmax)
+{
+    const int frame = blockIdx.y;
+    const float* d = disp + (size_t)frame * disp_frame;
+    float mn = INFINITY, mx = -INFINITY;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < npix; i += gridDim.x * blockDim.x) {
+        const float v = d[i];
+        mn = fminf(mn, v); mx = fmaxf(mx, v);
+    }
+    for (int o = 16; o; o >>= 1) {
+        mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicMin(minmax + 2 * frame, enc_ordered(mn));
+        atomicMin(minmax + 2 * frame + 1, ~enc_ordered(mx));
+    }
+}
+
+// ---- heatmap: heatmap() of FastACVNet_plus/test/main.cpp:7-24 -------------------------------------------------
+//   s = f32((max-min)/255)  [double arithmetic];  n = f32(f32(d - f32(min)) / s);  idx = sat_u8(round_half_even(|n|))
+template <bool VEC>
+__global__ void __launch_bounds__(256) heatmap_kernel(const float* __restrict__ disp, size_t disp_frame, int npix, const unsigned* __restrict__ minmax,
+                                                      uint8_t* __restrict__ out)
+{
+    __shared__ uint32_t s_jet[256];
+    __shared__ uint32_t s_w[8][96];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    s_jet[tid] = c_jet[tid];
+    __syncthreads();
+    const int frame = blockIdx.y;
+    const float mn = dec_ordered(minmax[2 * frame]), mx = dec_ordered(~minmax[2 * frame + 1]);
+    const float s = (float)(((double)mx - (double)mn) / 255.0);
+    const float* d = disp + (size_t)frame * disp_frame;
+    uint8_t* o = out + (size_t)frame * npix * 3;
+    const int p0 = (blockIdx.x * 256 + tid) * 4;
+    uint32_t px[4];
+    float v[4] = {0.f, 0.f, 0.f, 0.f};
+    if (VEC) { if (p0 < npix) { const float4 t = *reinterpret_cast<const float4*>(d + p0); v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w; } }
+    else { for (int k = 0; k < 4; k++) if (p0 + k < npix) v[k] = d[p0 + k]; }
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const float n = fabsf(__fdiv_rn(__fsub_rn(v[k], mn), s));
+        int idx = __float2int_rn(n);            // NaN -> 0, like saturate_cast<uchar>(cvRound(NaN) = INT_MIN)
+        idx = min(255, max(0, idx));
+        px[k] = s_jet[idx];
+    }
+    if (VEC) {
+        // 12 bytes per lane -> three coalesced 4-byte stores per lane through a warp-private transpose
+        uint32_t* sw = s_w[warp];
+        sw[lane * 3 + 0] = px[0] | (px[1] << 24);
+        sw[lane * 3 + 1] = (px[1] >> 8) | (px[2] << 16);
+        sw[lane * 3 + 2] = (px[2] >> 16) | (px[3] << 8);
+        __syncwarp();
+        const size_t w0 = (size_t)(blockIdx.x * 256 + warp * 32) * 3;   // first word of this warp
+        const size_t nwords = (size_t)npix * 3 / 4;
+        uint32_t* ow = reinterpret_cast<uint32_t*>(o);
+#pragma unroll
+        for (int m = 0; m < 3; m++) {
+            const size_t wi = w0 + lane + 32 * m;
+            if (wi < nwords) ow[wi] = sw[lane + 32 * m];
+        }
+    } else {
+        for (int k = 0; k < 4; k++)
+            if (p0 + k < npix) {
+                uint8_t* q = o + (size_t)(p0 + k) * 3;
+                q[0] = (uint8_t)px[k]; q[1] = (uint8_t)(px[k] >> 8); q[2] = (uint8_t)(px[k] >> 16);
+            }
+    }
+}
+
+// ---- synthetic disparity (stand-in for the TensorRT enqueue) ------------------------------------------------
+__device__ __forceinline__ uint32_t hash32(uint32_t x)
+{
+    x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
+    return x;
+}
+
+__global__ void __launch_bounds__(256) stub_kernel(float* __restrict__ disp, size_t disp_frame, int planes, int w, int h, int first_frame,
+                                                   unsigned seed, int negate)
+{
+    const int frame = blockIdx.y;
+    const size_t npix = (size_t)w * h;
+    const size_t p = (size_t)blockIdx.x * 256 + threadIdx.x;
+    if (p >= npix) return;
+    const int r = (int)(p / w), c = (int)(p - (size_t)r * w);
+    const int gframe = first_frame + frame;
+    float v = 4.0f + 60.0f * (0.5f + 0.5f * __sinf(6.2831853f * 3.0f * c / w + 0.37f * gframe)) * (0.5f + 0.5f * __cosf(6.2831853f * 2.0f * r / h));
+    const uint32_t u = hash32((uint32_t)p * 2654435761u ^ hash32(seed + 0x9e3779b9u * (uint32_t)gframe));
+    const uint32_t pm = u % 1000u;
+    if (pm < 50u) v = 0.0f;
+    else if (pm < 60u) v = -1.0f;
+    if (negate) v = -v;
+    float* d = disp + (size_t)frame * disp_frame;
+    d[p] = v;
+    for (int k = 1; k < planes; k++) d[(size_t)k * npix + p] = 0.0f;
+}
+
+__global__ void __launch_bounds__(256) copy_plane0_kernel(const float* __restrict__ disp, size_t disp_frame, size_t npix, float* __restrict__ out)
+{
+    const int frame = blockIdx.y;
+    const size_t p = (size_t)blockIdx.x * 256 + threadIdx.x;
+    if (p < npix) out[(size_t)frame * npix + p] = disp[(size_t)frame * disp_frame + p];
+}
+
+// ---- u8 resize (extension a8): OpenCV's fixed-point INTER_LINEAR for downscales ----------------------------
+__global__ void __launch_bounds__(256) resize_kernel(const ResizeArgs a)
+{
+    const int eye = blockIdx.y & 1, frame = blockIdx.y >> 1;
+    const size_t npix = (size_t)a.w * a.h;
+    const size_t p = (size_t)blockIdx.x * 256 + threadIdx.x;
+    if (p >= npix) return;
+    const int y = (int)(p / a.w), x = (int)(p - (size_t)y * a.w);
+    const uint8_t* src = (eye ? a.src[1] : a.src[0]) + (size_t)frame * a.src_frame;
+    uint8_t* dst = (eye ? a.dst[1] : a.dst[0]) + ((size_t)frame * npix + p) * 3;
+    if (a.area2x) {  // exact 2x decimation is executed by OpenCV as INTER_AREA: rounded mean of the 2x2 block
+        const uint8_t* r0 = src + (size_t)(2 * y) * a.src_pitch + 6 * x;
+        const uint8_t* r1 = r0 + a.src_pitch;
+#pragma unroll
+        for (int c = 0; c < 3; c++) dst[c] = (uint8_t)((r0[c] + r0[3 + c] + r1[c] + r1[3 + c] + 2) >> 2);
+        return;
+    }
+    const int x0 = a.tab_x[x], x1 = a.tab_x[a.w + x], a0 = a.tab_x[2 * a.w + x], a1 = a.tab_x[3 * a.w + x];
+    const int y0 = a.tab_y[y], y1 = a.tab_y[a.h + y], b0 = a.tab_y[2 * a.h + y], b1 = a.tab_y[3 * a.h + y];
+    const uint8_t* r0 = src + (size_t)y0 * a.src_pitch;
+    const uint8_t* r1 = src + (size_t)y1 * a.src_pitch;
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+        const int T0 = r0[3 * x0 + c] * a0 + r0[3 * x1 + c] * a1;
+        const int T1 = r1[3 * x0 + c] * a0 + r1[3 * x1 + c] * a1;
+        const int v = (((b0 * (T0 >> 4)) >> 16) + ((b1 * (T1 >> 4)) >> 16) + 2) >> 2;
+        dst[c] = (uint8_t)min(255, max(0, v));
+    }
+}
+
+}  // namespace
+
+cudaError_t launch_minmax(const float* disp, size_t disp_frame, int npix, int n, unsigned* minmax, cudaStream_t s, long* launches)
+{
+    if (n <= 0) return cudaSuccess;
+    int bx = (npix + 256 * 8 - 1) / (256 * 8);
+    if (bx < 1) bx = 1;
+    minmax_kernel<<<dim3((unsigned)bx, (unsigned)n), 256, 0, s>>>(disp, disp_frame, npix, minmax);
+    if (launches) ++*launches;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_heatmap(const float* disp, size_t disp_frame, int npix, int n, const unsigned* minmax, uint8_t* out, cudaStream_t s, long* launches)
+{
+    if (n <= 0) return cudaSuccess;
+    const bool vec = (npix % 4 == 0) && (disp_frame % 4 == 0) && (((uintptr_t)disp) % 16 == 0) && (((uintptr_t)out) % 4 == 0);
+    dim3 grid((unsigned)((npix + 1023) / 1024), (unsigned)n);
+    if (vec) heatmap_kernel<true><<<grid, 256, 0, s>>>(disp, disp_frame, npix, minmax, out);
+    else heatmap_kernel<false><<<grid, 256, 0, s>>>(disp, disp_frame, npix, minmax, out);
+    if (launches) ++*launches;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_stub(float* disp, size_t disp_frame, int planes, int w, int h, int first_frame, int n, unsigned seed, int negate, cudaStream_t s,
+                        long* launches)
+{
+    if (n <= 0) return cudaSuccess;
+    const size_t npix = (size_t)w * h;
+    stub_kernel<<<dim3((unsigned)((npix + 255) / 256), (unsigned)n), 256, 0, s>>>(disp, disp_frame, planes, w, h, first_frame, seed, negate);
+    if (launches) ++*launches;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_copy_plane0(const float* disp, size_t disp_frame, size_t npix, int n, float* out, cudaStream_t s, long* launches)
+{
+    if (n <= 0) return cudaSuccess;
+    copy_plane0_kernel<<<dim3((unsigned)((npix + 255) / 256), (unsigned)n), 256, 0, s>>>(disp, disp_frame, npix, out);
+    if (launches) ++*launches;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_resize(const ResizeArgs& a, cudaStream_t s, long* launches)
+{
+    if (a.n <= 0) return cudaSuccess;
+    const size_t npix = (size_t)a.w * a.h;
+    resize_kernel<<<dim3((unsigned)((npix + 255) / 256), 2u * (unsigned)a.n), 256, 0, s>>>(a);
+    if (launches) ++*launches;
+    return cudaGetLastError();
+}
+
+}  // namespace sa

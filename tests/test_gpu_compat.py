@@ -1,0 +1,110 @@
+"""The reference-named entry points (Initialize / Run<Model>[_RectifyImage] / Version / Release), used the way the
+reference's demo programs use them (FastACVNet_plus/test/main.cpp:27-74).  Needs a B200: -m gpu."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+CALIB = os.path.join(GOLDEN, "calib_b.yml")     # the */test/StereoCalibration.yml the demos load
+
+
+def _check_points(a, b):
+    assert np.array_equal(np.isnan(a), np.isnan(b)) and np.array_equal(np.isinf(a), np.isinf(b))
+    f = np.isfinite(b)
+    assert np.all(np.abs(a[f] - b[f]) <= 1e-5 * np.maximum(np.abs(a[f]), np.abs(b[f])))
+
+
+def test_demo_main_fastacvnet_plus(demo_pair, calibs, tmp_path):
+    from stereoalgorithms_b200 import compat
+    from stereoalgorithms_b200.compat import FastACVNet_plus as F, Mat
+    imageL, imageR = demo_pair
+    fastacvnet = F.Initialize("fast_acvnet_plus_generalization_opset16_480x640.onnx", 0, CALIB)
+    assert fastacvnet
+    assert F.Version(fastacvnet) == "FastACVNet_plus_Algorithm_V1.0"
+    pointcloud = np.empty(imageL.shape[1] * imageL.shape[0] * 6, np.float32)
+    disparity = Mat()
+    for _ in range(5):
+        imageL1, imageR1 = imageL.copy(), imageR.copy()
+        assert F.RunFastACVNet_plus_RectifyImage(fastacvnet, imageL1, imageR1, pointcloud, disparity) == 0
+    # left/right now hold the rectified images, as after cv::remap(img, img, ...)
+    c = calibs["calib_b"]
+    rl, rr = O.rectify_pair(c, imageL, imageR)
+    assert np.array_equal(imageL1, rl) and np.array_equal(imageR1, rr)
+    assert disparity.array.shape == (480, 640) and disparity.array.dtype == np.float32
+    want, _ = O.reproject_dense(O.FASTACVNET_PLUS, disparity.array, rl, c["Q"])
+    _check_points(pointcloud.reshape(-1, 6), want)
+    hm = compat.heatmap(fastacvnet, disparity)
+    assert np.array_equal(hm, O.heatmap(disparity.array))
+    # pointcloud.txt, first lines
+    path = str(tmp_path / "pointcloud.txt")
+    compat.write_pointcloud_txt(path, pointcloud[:6 * 1000])
+    with open(path) as f:
+        lines = f.read().splitlines()
+    assert lines == O.pointcloud_txt_lines(pointcloud.reshape(-1, 6), 1000)
+    # the no-rectify flavour leaves the images alone
+    a, b = imageL.copy(), imageR.copy()
+    assert F.RunFastACVNet_plus(fastacvnet, a, b, pointcloud, disparity) == 0
+    assert np.array_equal(a, imageL) and np.array_equal(b, imageR)
+    want, _ = O.reproject_dense(O.FASTACVNET_PLUS, disparity.array, imageL, c["Q"])
+    _check_points(pointcloud.reshape(-1, 6), want)
+    assert F.Release(fastacvnet) == 0
+
+
+@pytest.mark.parametrize("name", ["RAFTStereo", "HitNet", "CREStereo"])
+def test_other_models(demo_pair, calibs, name):
+    from stereoalgorithms_b200 import compat
+    M = getattr(compat, name)
+    run = {"RAFTStereo": "RunRAFTStereo", "HitNet": "RunHitNet", "CREStereo": "RunCREStereo_RectifyImage"}[name]
+    assert hasattr(M, "RunCREStereo") == (name == "CREStereo") and not hasattr(M, "RunRAFTStereo_RectifyImage")
+    p = M.Initialize("model.onnx", 0, CALIB)
+    assert M.Version(p) == {"RAFTStereo": "RAFTStereoAlgorithm_V1.0", "HitNet": "HitNetAlgorithm_V1.0", "CREStereo": "CREStereoAlgorithm_V1.0"}[name]
+    l, r = demo_pair[0].copy(), demo_pair[1].copy()
+    pc = np.empty(640 * 480 * 6, np.float32)
+    d = compat.Mat()
+    assert getattr(M, run)(p, l, r, pc, d) == 0
+    c = calibs["calib_b"]
+    rl, rr = O.rectify_pair(c, *demo_pair)
+    assert np.array_equal(l, rl) and np.array_equal(r, rr)                 # always-rectify entry points mutate in place
+    assert (d.array > 0).mean() > 0.9                                      # RAFT: returned disparity is the flipped, positive one
+    want, _ = O.reproject_dense(O.FASTACVNET_PLUS, d.array, rl, c["Q"])    # d is already the disparity as used
+    _check_points(pc.reshape(-1, 6), want)
+    assert M.Release(p) == 0
+
+
+def test_error_semantics(demo_pair, tmp_path):
+    from stereoalgorithms_b200.compat import CREStereo as M, Mat
+    pc = np.empty(640 * 480 * 6, np.float32)
+    d = Mat()
+    # missing calibration: Initialize still returns a handle (reference: prints a warning and goes on)
+    p = M.Initialize("m.onnx", 0, str(tmp_path / "nope.yml"))
+    assert p and "calibration_path does not exist" in M.LastError(p)
+    l, r = demo_pair[0].copy(), demo_pair[1].copy()
+    assert M.RunCREStereo_RectifyImage(p, l, r, pc, d) == -1               # cannot rectify without a calibration
+    assert M.RunCREStereo(p, None, r, pc, d) == -1                         # "Image_src is empty!!!"
+    assert M.RunCREStereo(p, np.empty((0, 0, 3), np.uint8), r, pc, d) == -1
+    assert M.Release(p) == 0
+    # failed init (no such GPU) latches: every Run returns -1
+    p = M.Initialize("m.onnx", 99, CALIB)
+    assert p
+    assert M.RunCREStereo(p, l, r, pc, d) == -1
+    assert M.Release(p) == 0
+
+
+def test_other_image_size_than_640x480(calibs):
+    """The reference asserts 640x480; here the geometry is re-created for the size it is given."""
+    from stereoalgorithms_b200.compat import FastACVNet_plus as F, Mat
+    W, H = 320, 240
+    img = O.synthetic_image(W, H, 1)
+    p = F.Initialize("m.onnx", 0, CALIB)
+    pc = np.empty(W * H * 6, np.float32)
+    d = Mat()
+    assert F.RunFastACVNet_plus(p, img.copy(), img.copy(), pc, d) == 0
+    assert d.array.shape == (H, W)
+    want, _ = O.reproject_dense(O.FASTACVNET_PLUS, d.array, img, calibs["calib_b"]["Q"])
+    _check_points(pc.reshape(-1, 6), want)
+    F.Release(p)

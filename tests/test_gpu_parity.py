@@ -1,0 +1,368 @@
+"""Parity of the CUDA path (through the C ABI) with the oracle and the golden vectors.  Needs a B200: -m gpu.
+
+Gates: maps, rectified u8, resized u8, heatmap, f16 tensors, point count and order: EXACT.
+f32 tensors and XYZ: |a-b| <= 1e-5 * max(|a|,|b|), inf/NaN equal in kind and position.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, md5, scaled_case
+from oracle import oracle as O
+from oracle import oracle_c as OC
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-5  # north_star: "normalised tensors and XYZ must fall within 1e-5 relative"
+
+
+def geom(*a, **k):
+    from stereoalgorithms_b200.geometry import StereoGeometry
+    return StereoGeometry(*a, **k)
+
+
+def assert_close_points(a, b, tag=""):
+    """1e-5 relative; inf/NaN must match in kind and position."""
+    a, b = np.asarray(a), np.asarray(b)
+    assert a.shape == b.shape, (tag, a.shape, b.shape)
+    assert np.array_equal(np.isnan(a), np.isnan(b)), tag + ": NaN positions differ"
+    assert np.array_equal(np.isposinf(a), np.isposinf(b)) and np.array_equal(np.isneginf(a), np.isneginf(b)), tag + ": inf positions differ"
+    fin = np.isfinite(b)
+    err = np.abs(a[fin] - b[fin])
+    tol = RTOL * np.maximum(np.abs(a[fin]), np.abs(b[fin]))
+    assert np.all(err <= tol), f"{tag}: max rel err {np.max(err / np.maximum(tol / RTOL, 1e-30))}"
+
+
+EYE_KEYS = (("intrinsic_left", "distCoeffs_left", "R_L", "P1"), ("intrinsic_right", "distCoeffs_right", "R_R", "P2"))
+
+
+# ---- a2: maps -----------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", ["calib_a", "calib_b", "calib_c_rational"])
+def test_maps_demo_bit_exact(golden, calibs, name):
+    g_ = golden["cases"]["demo_" + name]
+    with geom(640, 480) as g:
+        g.load_calibration_yaml(os.path.join(GOLDEN, name + ".yml"))
+        for eye, tag in ((0, "left"), (1, "right")):
+            m1, m2 = g.get_maps(eye)
+            assert md5(m1) == g_["map1_" + tag] and md5(m2) == g_["map2_" + tag]
+            k = EYE_KEYS[eye]
+            o1, o2 = O.init_undistort_rectify_map(*(calibs[name][x] for x in k), (640, 480))
+            assert np.array_equal(m1, o1) and np.array_equal(m2, o2)
+
+
+@pytest.mark.parametrize("name", ["kitti_1242x375", "hd_1920x1080", "hd_c_1920x1080", "uhd_3840x2160"])
+def test_maps_scaled_bit_exact(golden, calibs, name):
+    g_ = golden["cases"]["scaled_" + name]
+    c, (W, H) = scaled_case(calibs, name)
+    with geom(W, H) as g:
+        g.set_calibration(c)
+        for eye, tag in ((0, "left"), (1, "right")):
+            m1, m2 = g.get_maps(eye)
+            assert md5(m1) == g_["map1_" + tag] and md5(m2) == g_["map2_" + tag], (name, tag)
+
+
+@pytest.mark.parametrize("tag", ["absurd_fscale_0.02", "absurd_fscale_1e-7", "absurd_k1_+50"])
+def test_maps_absurd_calibrations(golden, calibs, tag):
+    g_ = golden["cases"][tag]
+    c = {k: np.array(v, copy=True) for k, v in calibs["calib_a"].items()}
+    c["P1"][0, 0] *= g_["fscale"]
+    c["P1"][1, 1] *= g_["fscale"]
+    c["distCoeffs_left"][0, 0] += g_["dk1"]
+    img = O.synthetic_image(640, 480, g_["image_seed"])
+    with geom(640, 480) as g:
+        g.set_calibration(c)
+        m1, m2 = g.get_maps(0)
+        assert md5(m1) == g_["map1"] and md5(m2) == g_["map2"]
+        # and the remap of a frame whose taps are (almost) all outside the image
+        g.rectify_preprocess(img[None], img[None])
+        assert md5(g.rectified(1, 0)[0]) == g_["rect"]
+
+
+# ---- a3: rectified images -------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", ["calib_a", "calib_b", "calib_c_rational"])
+@pytest.mark.parametrize("variant", ["default", "tile_fastest", "force_direct"])
+def test_rectified_demo_bit_exact(golden, demo_pair, name, variant):
+    g_ = golden["cases"]["demo_" + name]
+    l, r = demo_pair
+    with geom(640, 480, model="RAFTStereo") as g:
+        if variant == "force_direct":
+            g.set_option("force_direct", 1)
+        if variant == "tile_fastest":
+            g.set_option("frame_fastest", 0)
+        g.load_calibration_yaml(os.path.join(GOLDEN, name + ".yml"))
+        g.rectify_preprocess(l[None], r[None])
+        assert md5(g.rectified(1, 0)[0]) == g_["rect_left"]
+        assert md5(g.rectified(1, 1)[0]) == g_["rect_right"]
+
+
+@pytest.mark.parametrize("name", ["kitti_1242x375", "hd_1920x1080", "hd_c_1920x1080", "uhd_3840x2160"])
+def test_rectified_scaled_bit_exact(golden, calibs, name):
+    g_ = golden["cases"]["scaled_" + name]
+    c, (W, H) = scaled_case(calibs, name)
+    li, ri = O.synthetic_image(W, H, g_["image_seeds"][0]), O.synthetic_image(W, H, g_["image_seeds"][1])
+    with geom(W, H, model="CREStereo") as g:
+        g.set_calibration(c)
+        g.rectify_preprocess(li[None], ri[None])
+        assert md5(g.rectified(1, 0)[0]) == g_["rect_left"], name
+        assert md5(g.rectified(1, 1)[0]) == g_["rect_right"], name
+
+
+def test_rectified_batch_device_input_and_pitch(calibs, demo_pair):
+    """Batch of different frames, device-resident input (torch), then host input with a row pitch."""
+    import torch
+    c = calibs["calib_b"]
+    n = 5
+    rng = np.random.default_rng(3)
+    L = np.stack([np.clip(demo_pair[0].astype(np.int16) + rng.integers(-8, 9, demo_pair[0].shape), 0, 255).astype(np.uint8) for _ in range(n)])
+    R = np.stack([np.clip(demo_pair[1].astype(np.int16) + rng.integers(-8, 9, demo_pair[1].shape), 0, 255).astype(np.uint8) for _ in range(n)])
+    (l1, l2), (r1, r2) = O.rectify_maps(c, (640, 480))
+    want_l = np.stack([OC.remap(x, l1, l2) for x in L])
+    want_r = np.stack([OC.remap(x, r1, r2) for x in R])
+    with geom(640, 480, model="HitNet", max_batch=8) as g:
+        g.set_calibration(c)
+        g.rectify_preprocess(torch.from_numpy(L).cuda(), torch.from_numpy(R).cuda())
+        assert np.array_equal(g.rectified(n, 0), want_l) and np.array_equal(g.rectified(n, 1), want_r)
+        # pitched host rows (a cv::Mat ROI): 1920 -> 2000 bytes per row
+        Lp = np.zeros((n, 480, 2000), np.uint8)
+        Rp = np.zeros((n, 480, 2000), np.uint8)
+        Lp[:, :, :1920] = L.reshape(n, 480, 1920)
+        Rp[:, :, :1920] = R.reshape(n, 480, 1920)
+        g.rectify_preprocess(Lp, Rp, n=n, pitch=2000)
+        assert np.array_equal(g.rectified(n, 0), want_l) and np.array_equal(g.rectified(n, 1), want_r)
+
+
+# ---- a4 / a10: tensors -----------------------------------------------------------------------------------------
+@pytest.mark.parametrize("model", ["RAFTStereo", "HitNet", "CREStereo", "FastACVNet_plus"])
+@pytest.mark.parametrize("dtype", ["f32", "f16"])
+@pytest.mark.parametrize("rectify", [True, False])
+def test_tensors(calibs, demo_pair, model, dtype, rectify):
+    from stereoalgorithms_b200.geometry import F16, F32, MODELS
+    c = calibs["calib_a"]
+    l, r = demo_pair
+    npdt = np.float16 if dtype == "f16" else np.float32
+    rl, rr = O.rectify_pair(c, l, r) if rectify else (l, r)
+    want = O.preprocess(MODELS[model], rl, rr, npdt)
+    with geom(640, 480, model=model, dtype=F16 if dtype == "f16" else F32, max_batch=2) as g:
+        g.set_calibration(c)
+        g.rectify_preprocess(np.stack([l, l]), np.stack([r, r]), rectify=rectify)
+        if model == "HitNet":
+            t = g.tensor(2)
+            assert t.shape == (2, 6, 480, 640) and t.dtype == npdt
+            got = [t[0], t[1]]
+            want = [want, want]
+        else:
+            tl, tr = g.tensor(2, 0), g.tensor(2, 1)
+            got = [tl[0], tr[0], tl[1], tr[1]]
+            want = [want[0], want[1], want[0], want[1]]
+        for a, b in zip(got, want):
+            if dtype == "f16":
+                assert np.array_equal(a, b)                       # gate: exact
+            else:
+                assert np.all(np.abs(a - b) <= RTOL * np.maximum(np.abs(a), np.abs(b)))   # gate: 1e-5 relative
+                assert np.array_equal(a, b)                       # and in fact identical (LUT built the same way)
+
+
+# ---- a5 / a9: reprojection ---------------------------------------------------------------------------------------
+def _disp_input(model_id, W, H, seed):
+    d = O.synthetic_disparity(W, H, seed)
+    if model_id == O.RAFTSTEREO:
+        d = -d                                           # the network emits negative flow; the kernel flips it
+    if model_id == O.CRESTEREO:
+        return np.stack([d, np.full_like(d, 7.0)])       # 2 planes, plane 0 is the disparity
+    return d[None]
+
+
+@pytest.mark.parametrize("model", ["RAFTStereo", "HitNet", "CREStereo", "FastACVNet_plus"])
+@pytest.mark.parametrize("calib", ["calib_a", "calib_c_rational"])
+def test_reproject_dense_and_compact(calibs, demo_pair, model, calib):
+    from stereoalgorithms_b200.geometry import COMPACT, DENSE, MODELS
+    mid = MODELS[model]
+    c = calibs[calib]
+    l, r = demo_pair
+    n = 3
+    L, R = np.stack([l] * n), np.stack([r] * n)
+    D = np.stack([_disp_input(mid, 640, 480, 100 + i) for i in range(n)])
+    rl, _ = O.rectify_pair(c, l, r)
+    with geom(640, 480, model=model, max_batch=4) as g:
+        g.set_calibration(c)
+        g.rectify_preprocess(L, R)
+        g.set_disparity(D)
+        pts, cnt = g.reproject(n, DENSE)
+        dout = g.disparity(n)
+        assert list(cnt) == [640 * 480] * n
+        for i in range(n):
+            want, dw = O.reproject_dense(mid, D[i, 0], rl, c["Q"])
+            assert_close_points(pts[i], want, f"{model} dense frame {i}")
+            assert np.array_equal(pts[i][:, 3:], want[:, 3:])                 # colours exact
+            assert np.array_equal(dout[i], dw)                                # RAFT: flipped and written back
+        # compact (extension): count and order exact
+        g.set_disparity(D)
+        cp, cc = g.reproject(n, COMPACT)
+        for i in range(n):
+            want, k, _ = O.reproject_compact(mid, D[i, 0], rl, c["Q"])
+            assert cc[i] == k and 0 < k < 640 * 480
+            assert_close_points(cp[i, :k], want, f"{model} compact frame {i}")
+            assert np.array_equal(cp[i, :k].view(np.uint32), want.view(np.uint32))   # identical bits -> identical order
+            assert not cp[i, k:].any()                                          # nothing written past the count
+
+
+@pytest.mark.parametrize("size", [(1242, 375), (322, 241), (64, 16), (5, 3)])
+def test_reproject_odd_sizes(calibs, size):
+    """Pixel counts that are not multiples of 4 / 1024: scalar paths, partial warps, rows that straddle a thread."""
+    from stereoalgorithms_b200.geometry import COMPACT, DENSE
+    W, H = size
+    c = O.scale_calibration(calibs["calib_a"], W / 640)
+    rng = np.random.default_rng(W * H)
+    img = rng.integers(0, 256, (2, H, W, 3), dtype=np.uint8)
+    d = rng.normal(20, 15, (2, 1, H, W)).astype(np.float32)
+    d[rng.random(d.shape) < 0.1] = 0
+    with geom(W, H, model="FastACVNet_plus", max_batch=2) as g:
+        g.set_calibration(c)
+        g.rectify_preprocess(img, img, rectify=False)
+        g.set_disparity(d)
+        pts, _ = g.reproject(2, DENSE)
+        cp, cc = g.reproject(2, COMPACT)
+        heat = g.heatmap(2)
+        for i in range(2):
+            want, _ = O.reproject_dense(O.FASTACVNET_PLUS, d[i, 0], img[i], c["Q"])
+            assert_close_points(pts[i], want, f"{size} dense")
+            wc, k, _ = O.reproject_compact(O.FASTACVNET_PLUS, d[i, 0], img[i], c["Q"])
+            assert cc[i] == k
+            assert np.array_equal(cp[i, :k].view(np.uint32), wc.view(np.uint32))
+            assert np.array_equal(heat[i], O.heatmap(d[i, 0]))
+
+
+def test_reproject_general_Q(calibs, demo_pair):
+    """A Q with every used entry non-trivial: products are no longer exact, hence the 1e-5 gate."""
+    from stereoalgorithms_b200.geometry import DENSE
+    c = calibs["calib_a"]
+    Q = np.array([[1.01, 0.02, 0, -295.1], [-0.03, 0.99, 0, -274.7], [0.001, -0.002, 0, 541.6], [0, 0, 0.01663, 0.1]])
+    d = O.synthetic_disparity(640, 480, 5)
+    with geom(640, 480) as g:
+        g.set_calibration(c)
+        g.set_Q(Q)
+        g.rectify_preprocess(demo_pair[0][None], demo_pair[1][None], rectify=False)
+        g.set_disparity(d[None, None])
+        pts, _ = g.reproject(1, DENSE)
+        want, _ = O.reproject_dense(O.FASTACVNET_PLUS, d, demo_pair[0], Q)
+        assert_close_points(pts[0], want, "general Q")
+        assert np.array_equal(g.get_Q(), Q)
+
+
+# ---- a6: heatmap ---------------------------------------------------------------------------------------------------
+def test_heatmap_golden(golden):
+    cases = {"synthetic_640x480": O.synthetic_disparity(640, 480, 1234),
+             "synthetic_noinvalid": O.synthetic_disparity(640, 480, 1, invalid=False),
+             "negated": -O.synthetic_disparity(320, 240, 5),
+             "constant": np.full((48, 64), 3.25, np.float32),
+             "random": np.random.default_rng(9).normal(30, 20, (375, 1242)).astype(np.float32)}
+    for tag, d in cases.items():
+        H, W = d.shape
+        with geom(W, H, model="HitNet") as g:
+            g.set_disparity(d[None, None])
+            hm = g.heatmap(1)                      # standalone min/max pass
+            assert md5(hm[0]) == golden["heatmap"][tag]["md5"], tag
+
+
+def test_heatmap_after_reproject_uses_fused_minmax(calibs, demo_pair):
+    from stereoalgorithms_b200.geometry import DENSE
+    d = np.stack([O.synthetic_disparity(640, 480, 40 + i) * (1 + i) for i in range(3)])
+    with geom(640, 480, model="RAFTStereo", max_batch=3) as g:
+        g.set_calibration(calibs["calib_a"])
+        g.rectify_preprocess(np.stack([demo_pair[0]] * 3), np.stack([demo_pair[1]] * 3))
+        g.set_disparity(-d[:, None])
+        before = g.launch_count
+        g.reproject(3, DENSE, to_host=False)
+        hm = g.heatmap(3)
+        assert g.launch_count - before == 2          # reproject + heatmap, no separate min/max launch
+        for i in range(3):
+            assert np.array_equal(hm[i], O.heatmap(d[i])), i   # on the flipped (positive) disparity
+
+
+# ---- a8: resize path -------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("src,dst", [((1920, 1080), (640, 480)), ((1280, 960), (640, 480)), ((1242, 375), (640, 192))])
+def test_resize_path(calibs, src, dst):
+    from stereoalgorithms_b200.geometry import DENSE
+    W, H = src
+    s = W / 640
+    c = O.scale_calibration(calibs["calib_a"], s, crop_y=(480 * s - H) / 2)
+    li, ri = O.synthetic_image(W, H, 50), O.synthetic_image(W, H, 51)
+    d = O.synthetic_disparity(dst[0], dst[1], 52)
+    ref = O.run_pair(O.FASTACVNET_PLUS, c, li, ri, d, net_size=dst)
+    with geom(W, H, model="FastACVNet_plus", net_size=dst) as g:
+        g.set_calibration(c)
+        g.rectify_preprocess(li[None], ri[None])
+        assert np.array_equal(g.rectified(1, 0)[0], ref["rect_left"])
+        assert np.array_equal(g.net_image(1, 0)[0], ref["net_left"]) and np.array_equal(g.net_image(1, 1)[0], ref["net_right"])
+        assert np.array_equal(g.tensor(1, 0)[0], ref["tensors"][0]) and np.array_equal(g.tensor(1, 1)[0], ref["tensors"][1])
+        g.set_disparity(d[None, None])
+        pts, _ = g.reproject(1, DENSE)
+        assert_close_points(pts[0], ref["points"], "resize path")
+
+
+# ---- a7: the whole Run flow with host buffers ----------------------------------------------------------------------
+@pytest.mark.parametrize("model", ["RAFTStereo", "FastACVNet_plus"])
+def test_run_batch_host_to_host(calibs, demo_pair, model):
+    from stereoalgorithms_b200.geometry import MODELS, PinnedArray
+    mid = MODELS[model]
+    c = calibs["calib_a"]
+    n = 11                                            # not a multiple of the chunk size
+    rng = np.random.default_rng(8)
+    L = np.stack([np.roll(demo_pair[0], i * 7, axis=1) for i in range(n)])
+    R = np.stack([np.roll(demo_pair[1], i * 7, axis=1) for i in range(n)])
+    D = np.stack([_disp_input(mid, 640, 480, 200 + i) for i in range(n)])
+    pin = [PinnedArray(L.shape, np.uint8), PinnedArray(R.shape, np.uint8), PinnedArray((n, 640 * 480, 6), np.float32),
+           PinnedArray((n, 480, 640), np.float32), PinnedArray(L.shape, np.uint8), PinnedArray(R.shape, np.uint8),
+           PinnedArray((n, 480, 640, 3), np.uint8)]
+    pin[0].array[:] = L
+    pin[1].array[:] = R
+    with geom(640, 480, model=model, max_batch=16) as g:
+        g.set_calibration(c)
+        g.set_option("chunk", 4)
+        g.set_disparity(D)
+        g.run_batch(pin[0].array, pin[1].array, n, rectify=True, stub_seed=0, pointcloud=pin[2].array, disparity=pin[3].array,
+                    rect_left=pin[4].array, rect_right=pin[5].array, heatmap=pin[6].array)
+        for i in range(n):
+            ref = O.run_pair(mid, c, L[i], R[i], D[i, 0])
+            assert np.array_equal(pin[4].array[i], ref["rect_left"]) and np.array_equal(pin[5].array[i], ref["rect_right"])
+            assert_close_points(pin[2].array[i], ref["points"], f"run_batch {i}")
+            assert np.array_equal(pin[3].array[i], ref["disparity"])
+            assert np.array_equal(pin[6].array[i], ref["heatmap"])
+        # the stub engine produces a usable disparity too (~5 % zeros, ~1 % negatives after the RAFT flip)
+        g.run_batch(pin[0].array, pin[1].array, n, rectify=True, stub_seed=7, pointcloud=pin[2].array, disparity=pin[3].array)
+        dd = pin[3].array
+        assert 0.03 < (dd == 0).mean() < 0.07 and 0.005 < (dd < 0).mean() < 0.015 and dd.max() < 65
+        ref_pts, _ = O.reproject_dense(O.FASTACVNET_PLUS, dd[2], O.rectify_pair(c, L[2], R[2])[0], c["Q"])
+        assert_close_points(pin[2].array[2], ref_pts, "stub frame 2")
+
+
+# ---- errors ----------------------------------------------------------------------------------------------------------
+def test_error_behaviour(demo_pair, tmp_path):
+    from stereoalgorithms_b200 import _lib as L
+    from stereoalgorithms_b200.geometry import DENSE, StereoGeomError
+    l, r = demo_pair
+    with geom(640, 480, max_batch=1) as g:
+        with pytest.raises(StereoGeomError) as e:
+            g.rectify_preprocess(l[None], r[None])                      # no calibration yet
+        assert e.value.code == L.SA_ERR_NOT_READY
+        with pytest.raises(StereoGeomError) as e:
+            g.rectify_preprocess(np.stack([l, l]), np.stack([r, r]))    # n > max_batch
+        assert e.value.code == L.SA_ERR_TOO_LARGE
+        with pytest.raises(StereoGeomError) as e:
+            g.load_calibration_yaml(str(tmp_path / "missing.yml"))
+        assert e.value.code == L.SA_ERR_IO
+        bad = tmp_path / "bad.yml"
+        bad.write_text("%YAML:1.0\nQ: !!opencv-matrix\n   rows: 4\n   cols: 4\n   dt: d\n   data: [ 1., 2. ]\n")
+        with pytest.raises(StereoGeomError) as e:
+            g.load_calibration_yaml(str(bad))
+        assert e.value.code == L.SA_ERR_PARSE
+        g.rectify_preprocess(l[None], r[None], rectify=False)
+        with pytest.raises(StereoGeomError) as e:
+            g.reproject(1, DENSE)                                       # no Q
+        assert e.value.code == L.SA_ERR_NOT_READY
+        assert g.rectify_preprocess(l[:0][None], r[:0][None], n=0) == 0  # empty batch is a no-op
+    with pytest.raises(StereoGeomError):
+        geom(640, 480, net_size=(1280, 960))                             # upscaling is not supported
+    with pytest.raises(StereoGeomError):
+        geom(0, 480)

@@ -1,0 +1,153 @@
+"""Host-side logic of the C-ABI library that needs no GPU: symbol surface, calibration parser, normalisation and
+resize tables, point-cloud writer, and the "fails loudly without a device" contract.  CPU only."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, ROOT
+from oracle import oracle as O
+
+
+@pytest.fixture(scope="module")
+def lib():
+    from stereoalgorithms_b200 import _lib
+    return _lib.load()
+
+
+def _declared_symbols():
+    names = []
+    for hdr in ("stereo_geom.h", "stereo_algorithms_compat.h"):
+        text = open(os.path.join(ROOT, "include", hdr)).read()
+        text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+        names += re.findall(r"SA_API\s+[^;(]*?\b(sa_\w+)\s*\(", text)
+    return names
+
+
+def test_library_exports_every_declared_symbol(lib):
+    from stereoalgorithms_b200 import _lib
+    declared = _declared_symbols()
+    assert len(declared) >= 40 and len(set(declared)) == len(declared)
+    for name in declared:
+        assert hasattr(lib, name), f"{name} is declared in include/ but not exported"
+        assert name in _lib.SIGNATURES, f"{name} has no ctypes signature"
+    assert set(_lib.SIGNATURES) == set(declared)
+    assert lib.sa_version().startswith(b"stereo_geom_b200")
+
+
+def _parse(lib, path):
+    from stereoalgorithms_b200._lib import sa_calibration
+    c = sa_calibration()
+    err = C.create_string_buffer(512)
+    rc = lib.sa_parse_calibration_yaml(path.encode(), C.byref(c), err, 512)
+    return rc, c, err.value.decode()
+
+
+@pytest.mark.parametrize("name", ["calib_a", "calib_b", "calib_b_alt", "calib_c_rational"])
+def test_calibration_parser_matches_oracle_parser(lib, name):
+    path = os.path.join(GOLDEN, name + ".yml")
+    rc, c, err = _parse(lib, path)
+    assert rc == 0, err
+    want = O.load_calibration_yaml(path)
+    pairs = {"K_l": "intrinsic_left", "K_r": "intrinsic_right", "R_L": "R_L", "R_R": "R_R", "P1": "P1", "P2": "P2", "Q": "Q", "R": "R", "T": "T"}
+    for f, k in pairs.items():
+        assert np.array_equal(np.array(getattr(c, f)), want[k].ravel()), (name, k)      # bit-exact doubles
+    nl, nr = want["distCoeffs_left"].size, want["distCoeffs_right"].size
+    assert (c.nD_l, c.nD_r) == (nl, nr) and nl in (5, 8)
+    assert np.array_equal(np.array(c.D_l)[:nl], want["distCoeffs_left"].ravel()) and not np.array(c.D_l)[nl:].any()
+    assert np.array_equal(np.array(c.D_r)[:nr], want["distCoeffs_right"].ravel())
+
+
+def test_calibration_parser_variants_and_errors(lib, tmp_path):
+    base = open(os.path.join(GOLDEN, "calib_a.yml")).read()
+    # no "---", no space after '[', no trailing newline, CRLF-free numbers like "0." and "1.", reordered + unknown keys
+    body = base.replace("---\n", "").replace("data: [ ", "data: [").rstrip("\n")
+    body = "%YAML:1.0\nvalidROIL: [ 0, 0, 640, 480 ]\nfoo: 3\n" + body.split("\n", 1)[1] + "\nvalidROIR: [ 0, 0, 640, 480 ]"
+    p = tmp_path / "variant.yml"
+    p.write_text(body)
+    rc, c, err = _parse(lib, str(p))
+    assert rc == 0, err
+    want = O.load_calibration_yaml(os.path.join(GOLDEN, "calib_a.yml"))
+    assert np.array_equal(np.array(c.Q), want["Q"].ravel()) and np.array_equal(np.array(c.K_l), want["intrinsic_left"].ravel())
+    # errors
+    from stereoalgorithms_b200 import _lib as L
+    rc, _, err = _parse(lib, str(tmp_path / "missing.yml"))
+    assert rc == L.SA_ERR_IO and "cannot open" in err
+    (tmp_path / "short.yml").write_text(base.replace("rows: 4", "rows: 5"))
+    rc, _, err = _parse(lib, str(tmp_path / "short.yml"))
+    assert rc == L.SA_ERR_PARSE and "Q" in err
+    (tmp_path / "nonum.yml").write_text(base.replace("1., 0., 0.,", "1., zero, 0.,", 1))
+    rc, _, err = _parse(lib, str(tmp_path / "nonum.yml"))
+    assert rc == L.SA_ERR_PARSE
+    (tmp_path / "noq.yml").write_text(base[:base.index("Q: !!opencv-matrix")])
+    rc, _, err = _parse(lib, str(tmp_path / "noq.yml"))
+    assert rc == L.SA_ERR_PARSE and "'Q'" in err
+    (tmp_path / "unterminated.yml").write_text(base[:base.rindex("]")])
+    rc, _, err = _parse(lib, str(tmp_path / "unterminated.yml"))
+    assert rc == L.SA_ERR_PARSE
+
+
+@pytest.mark.parametrize("model", [0, 1, 2, 3])
+def test_norm_lut_matches_oracle(lib, model):
+    lut = np.empty((3, 256), np.float32)
+    assert lib.sa_norm_lut(model, lut.ctypes.data) == 0
+    assert np.array_equal(lut.view(np.uint32), O.norm_lut(model).view(np.uint32))
+    assert lib.sa_norm_lut(7, lut.ctypes.data) != 0
+
+
+@pytest.mark.parametrize("dst,src", [(640, 1920), (480, 1080), (640, 1242), (192, 375), (1248, 1920), (640, 640), (3, 1000)])
+def test_resize_table_matches_oracle(lib, dst, src):
+    t = np.empty((4, dst), np.int32)
+    assert lib.sa_resize_table(dst, src, t.ctypes.data) == 0
+    s0, s1, c0, c1 = O._resize_axis_tab(dst, src)
+    assert np.array_equal(t[0], s0) and np.array_equal(t[1], s1) and np.array_equal(t[2], c0) and np.array_equal(t[3], c1)
+    assert np.all(t[2] + t[3] == 2048)
+
+
+def test_pointcloud_txt_writer(lib, tmp_path):
+    pts = np.array([[1.5, -0.25, 1e-7, 255, 0, 12], [np.inf, -np.inf, np.nan, 1, 2, 3], [123456.789, 1e10, 3.0, 0, 0, 0],
+                    [0.1, 1 / 3, -2 / 3, 7, 8, 9]], np.float32)
+    path = str(tmp_path / "pointcloud.txt")
+    assert lib.sa_write_pointcloud_txt(path.encode(), pts.ctypes.data, len(pts)) == 0
+    lines = open(path).read().splitlines()
+    want = O.pointcloud_txt_lines(pts)
+    # C++ streams print nan/inf like printf; the sign of nan is platform noise
+    assert [l.replace("-nan", "nan") for l in lines] == want
+    assert lib.sa_write_pointcloud_txt(str(tmp_path / "no" / "dir.txt").encode(), pts.ctypes.data, 1) != 0
+
+
+def _no_gpu():
+    try:
+        import torch
+        return not torch.cuda.is_available()
+    except Exception:
+        return True
+
+
+@pytest.mark.skipif(not _no_gpu(), reason="only meaningful on a box without a GPU")
+def test_fails_loudly_without_a_device(lib):
+    from stereoalgorithms_b200 import _lib as L
+    from stereoalgorithms_b200.geometry import StereoGeomError, StereoGeometry
+    with pytest.raises(StereoGeomError) as e:
+        StereoGeometry(640, 480)
+    assert e.value.code == L.SA_ERR_CUDA and "no CPU fallback" in str(e.value)
+    # the reference-named API keeps the reference's semantics: a handle comes back, Run reports -1
+    from stereoalgorithms_b200.compat import FastACVNet_plus as F, Mat
+    p = F.Initialize("m.onnx", 0, os.path.join(GOLDEN, "calib_b.yml"))
+    assert p
+    img = np.zeros((480, 640, 3), np.uint8)
+    assert F.RunFastACVNet_plus_RectifyImage(p, img, img.copy(), np.empty(640 * 480 * 6, np.float32), Mat()) == -1
+    assert F.Version(p) == "FastACVNet_plus_Algorithm_V1.0"
+    assert F.Release(p) == 0
+
+
+def test_product_does_not_import_the_oracle():
+    """No file of the product package may reference oracle/ (a product path through the oracle voids parity)."""
+    pkg = os.path.join(ROOT, "stereoalgorithms_b200")
+    for root, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cpp", ".h")):
+                text = open(os.path.join(root, f)).read()
+                assert "oracle" not in text.lower(), f"{f} mentions the oracle"
