@@ -255,8 +255,10 @@ def main():
     g.stub_disparity(n, seed=1234 + rank)
     g.synchronize()
 
-    stream = torch.cuda.current_stream()
+    stream = torch.cuda.Stream()                              # a real (non-null) stream: NULL would mean "the handle's own stream"
+    torch.cuda.set_stream(stream)
     sp = stream.cuda_stream                                   # every kernel of the step is launched on this stream
+    assert sp != 0
 
     def step():
         g.rectify_preprocess(dL, dR, n=n, stream=sp)

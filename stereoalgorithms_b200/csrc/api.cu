@@ -179,6 +179,7 @@ static int stage_rectify(sa_handle* h, int f0, int n, const uint8_t* src_l, cons
         a.W = h->W; a.H = h->H; a.n = n; a.model = h->cfg.model; a.dtype = h->cfg.tensor_dtype;
         a.write_tensor = h->resize ? 0 : 1;
         a.frame_fastest = (int)h->opt_frame_fastest;
+        a.force_generic = (int)h->opt_force_generic;
         {
             StageScope t(h, SA_STAGE_RECTIFY, s);
             SA_CUDA(h, launch_rectify(a, s, &h->launches));
@@ -240,13 +241,13 @@ static int stage_reproject(sa_handle* h, int f0, int n, int mode, float* dev_out
     a.w = h->w; a.h = h->h; a.n = n;
     a.negate = h->cfg.model == SA_MODEL_RAFTSTEREO;
     a.compact = mode == SA_COMPACT;
-    a.minmax = h->minmax + 2 * (size_t)f0;
+    a.exact_div = (int)h->opt_exact_div;
     const int nblk = reproject_blocks_per_frame(h->w, h->h);
+    a.blk_minmax = h->blk_minmax + 2 * (size_t)f0 * nblk;
     a.blk_counts = h->blk_counts + (size_t)f0 * nblk;
     a.blk_offsets = h->blk_offsets + (size_t)f0 * nblk;
     a.counts = dev_counts;
     (void)npix;
-    SA_CUDA(h, cudaMemsetAsync(a.minmax, 0xff, sizeof(unsigned) * 2 * (size_t)n, s));
     {
         StageScope t(h, SA_STAGE_REPROJECT, s);
         SA_CUDA(h, launch_reproject(a, s, &h->launches));
@@ -254,13 +255,17 @@ static int stage_reproject(sa_handle* h, int f0, int n, int mode, float* dev_out
     return SA_OK;
 }
 
-static int stage_heatmap(sa_handle* h, int f0, int n, uint8_t* dev_out /* frame f0 */, bool minmax_current, cudaStream_t s)
+// minmax_state: 2 = the final per-frame min/max is current, 1 = only reproject's per-CTA partials are, 0 = neither
+static int stage_heatmap(sa_handle* h, int f0, int n, uint8_t* dev_out /* frame f0 */, int minmax_state, cudaStream_t s)
 {
     const int npix = h->w * h->h;
     const float* d = h->disp + (size_t)f0 * disp_frame_floats(h);
     unsigned* mm = h->minmax + 2 * (size_t)f0;
     StageScope t(h, SA_STAGE_HEATMAP, s);
-    if (!minmax_current) {
+    if (minmax_state == 1) {
+        const int nblk = reproject_blocks_per_frame(h->w, h->h);
+        SA_CUDA(h, launch_reduce_minmax(h->blk_minmax + 2 * (size_t)f0 * nblk, nblk, n, mm, s, &h->launches));
+    } else if (minmax_state == 0) {
         SA_CUDA(h, cudaMemsetAsync(mm, 0xff, sizeof(unsigned) * 2 * (size_t)n, s));
         SA_CUDA(h, launch_minmax(d, disp_frame_floats(h), npix, n, mm, s, &h->launches));
     }
@@ -337,6 +342,7 @@ int sa_create(const sa_config* cfg, sa_handle** out)
     A(dev_alloc(&h->minmax, N * 2));
     A(dev_alloc(&h->blk_counts, N * nblk));
     A(dev_alloc(&h->blk_offsets, N * nblk));
+    A(dev_alloc(&h->blk_minmax, N * nblk * 2));
     A(dev_alloc(&h->lut32, 768));
     A(dev_alloc(&h->lut16, 768));
     if (h->resize) { A(dev_alloc(&h->rs_x, 4 * (size_t)h->w)); A(dev_alloc(&h->rs_y, 4 * (size_t)h->h)); }
@@ -379,7 +385,7 @@ int sa_destroy(sa_handle* h)
         cudaFree(h->raw[e]); cudaFree(h->rect[e]); cudaFree(h->net_u8[e]); cudaFree(h->map1[e]); cudaFree(h->map2[e]); cudaFree(h->tiles[e]);
     }
     cudaFree(h->tensor[0]); cudaFree(h->disp); cudaFree(h->points); cudaFree(h->heat); cudaFree(h->counts); cudaFree(h->minmax);
-    cudaFree(h->blk_counts); cudaFree(h->blk_offsets); cudaFree(h->lut32); cudaFree(h->lut16); cudaFree(h->rs_x); cudaFree(h->rs_y);
+    cudaFree(h->blk_counts); cudaFree(h->blk_offsets); cudaFree(h->blk_minmax); cudaFree(h->lut32); cudaFree(h->lut16); cudaFree(h->rs_x); cudaFree(h->rs_y);
     for (int s = 0; s < SA_STAGE_COUNT_; s++) {
         for (auto ev : h->timer.begin[s]) cudaEventDestroy(ev);
         for (auto ev : h->timer.end[s]) cudaEventDestroy(ev);
@@ -544,6 +550,7 @@ int sa_rectify_preprocess(sa_handle* h, int n, const uint8_t* left, const uint8_
     }
     h->n_last = n;
     h->minmax_valid = 0;
+    h->partial_valid = 0;
     return stage_rectify(h, 0, n, src[0], src[1], src_pitch, src_pitch * h->H, rectify, s);
 }
 
@@ -558,6 +565,7 @@ int sa_stub_disparity(sa_handle* h, int n, unsigned seed, sa_stream stream)
     SA_CHECK_N(h, n);
     cudaStream_t s = pick(h, stream);
     h->minmax_valid = 0;
+    h->partial_valid = 0;
     StageScope t(h, SA_STAGE_STUB, s);
     SA_CUDA(h, launch_stub(h->disp, disp_frame_floats(h), h->planes, h->w, h->h, 0, n, seed, h->cfg.model == SA_MODEL_RAFTSTEREO, s, &h->launches));
     return SA_OK;
@@ -570,6 +578,7 @@ int sa_set_disparity(sa_handle* h, int n, const float* disparity, int where, sa_
     if (!disparity) return fail(h, SA_ERR_INVALID_ARG, "sa_set_disparity: null");
     cudaStream_t s = pick(h, stream);
     h->minmax_valid = 0;
+    h->partial_valid = 0;
     SA_CUDA(h, cudaMemcpyAsync(h->disp, disparity, (size_t)n * disp_frame_floats(h) * sizeof(float),
                                where == SA_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice, s));
     if (where == SA_HOST) SA_CUDA(h, cudaStreamSynchronize(s));  // the caller may reuse its buffer
@@ -590,7 +599,8 @@ int sa_reproject(sa_handle* h, int n, int mode, float* out, int* counts, int whe
     int* dev_counts = (counts && where == SA_DEVICE) ? counts : (counts ? h->counts : nullptr);
     int rc = stage_reproject(h, 0, n, mode, dev, dev_counts, s);
     if (rc != SA_OK) return rc;
-    h->minmax_valid = n;
+    h->minmax_valid = 0;
+    h->partial_valid = n;
     if (where == SA_HOST && (out || counts)) {
         if (mode == SA_DENSE) {
             if (counts) for (int i = 0; i < n; i++) counts[i] = (int)npix;
@@ -618,9 +628,9 @@ int sa_heatmap(sa_handle* h, int n, uint8_t* out, int where, sa_stream stream)
     cudaStream_t s = pick(h, stream);
     uint8_t* dev = (out && where == SA_DEVICE) ? out : h->heat;
     if (!dev) return fail(h, SA_ERR_INVALID_ARG, "sa_heatmap: no internal heatmap buffer (SA_FLAG_NO_HEATMAP_BUF) and no device `out`");
-    int rc = stage_heatmap(h, 0, n, dev, h->minmax_valid >= n, s);
+    int rc = stage_heatmap(h, 0, n, dev, h->minmax_valid >= n ? 2 : (h->partial_valid >= n ? 1 : 0), s);
     if (rc != SA_OK) return rc;
-    h->minmax_valid = n > h->minmax_valid ? n : h->minmax_valid;
+    h->minmax_valid = n;
     if (out && where == SA_HOST) return copy_out(h, out, dev, (size_t)n * h->w * h->h * 3, SA_HOST, s);
     return SA_OK;
 }
@@ -715,6 +725,7 @@ int sa_run_batch(sa_handle* h, int n, const uint8_t* left, const uint8_t* right,
     const int nchunks = (n + chunk - 1) / chunk;
     h->n_last = n;
     h->minmax_valid = 0;
+    h->partial_valid = 0;
     uint8_t* rect_out[2] = {rect_left, rect_right};
     const uint8_t* host_in[2] = {left, right};
     for (int c = 0; c < nchunks; c++) {
@@ -742,7 +753,7 @@ int sa_run_batch(sa_handle* h, int n, const uint8_t* left, const uint8_t* right,
         // stage B (+ C)
         rc = stage_reproject(h, f0, m, SA_DENSE, h->points + (size_t)f0 * npix * 6, nullptr, h->stream);
         if (rc != SA_OK) return rc;
-        if (heatmap) { rc = stage_heatmap(h, f0, m, h->heat + (size_t)f0 * npix * 3, true, h->stream); if (rc != SA_OK) return rc; }
+        if (heatmap) { rc = stage_heatmap(h, f0, m, h->heat + (size_t)f0 * npix * 3, 1, h->stream); if (rc != SA_OK) return rc; }
         SA_CUDA(h, cudaEventRecord(done, h->stream));
         SA_CUDA(h, cudaStreamWaitEvent(h->s_d2h, done, 0));
         // download (cudaMemcpy D2H x2, TRTFastACVNet_plus.cpp:163-164; plus the rectified images the reference leaves in left/right)
@@ -756,7 +767,8 @@ int sa_run_batch(sa_handle* h, int n, const uint8_t* left, const uint8_t* right,
     // colour / rectified pointers describe frame 0 of the whole batch
     SA_CUDA(h, cudaStreamSynchronize(h->s_d2h));
     SA_CUDA(h, cudaStreamSynchronize(h->stream));
-    h->minmax_valid = n;
+    h->partial_valid = n;
+    h->minmax_valid = heatmap ? n : 0;
     return SA_OK;
 }
 
@@ -809,6 +821,8 @@ int sa_set_option(sa_handle* h, const char* key, long value)
     if (!std::strcmp(key, "frame_fastest")) h->opt_frame_fastest = value;
     else if (!std::strcmp(key, "chunk")) h->opt_chunk = value;
     else if (!std::strcmp(key, "force_direct")) h->opt_force_direct = value;   // takes effect at the next map computation
+    else if (!std::strcmp(key, "force_generic")) h->opt_force_generic = value;
+    else if (!std::strcmp(key, "exact_div")) h->opt_exact_div = value;
     else return fail(h, SA_ERR_INVALID_ARG, "sa_set_option: unknown key '%s'", key);
     return SA_OK;
 }

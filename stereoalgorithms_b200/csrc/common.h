@@ -24,9 +24,12 @@ constexpr int kFootprintWords = 3072;  // staged source pixels per tile (BGRx wo
 // (BORDER_CONSTANT 0).  w == 0 marks a tile whose footprint does not fit kFootprintWords: it is
 // gathered directly from global memory.
 struct TileInfo {
-    short x0, y0;  // top-left (x0 is a multiple of 4)
-    short w, h;    // extent (w is a multiple of 4)
+    short x0, y0;      // top-left (x0 is a multiple of 4)
+    short w, h;        // extent (w is a multiple of 4)
+    uint32_t inv_gw;   // ceil(2^20 / (w/4)): exact division of a group index < 768 by the groups per row
+    uint32_t flags;    // kTileInterior: the whole footprint lies inside the image
 };
+constexpr uint32_t kTileInterior = 1u;
 
 struct MapParams {
     double iR[9];
@@ -75,6 +78,7 @@ struct sa_handle {
     __half* lut16 = nullptr;
     unsigned* minmax = nullptr;               // [N][2] ordered-uint encodings (min, ~max)
     int* blk_counts = nullptr;                // [N][blocks per frame]  (compaction scratch)
+    unsigned* blk_minmax = nullptr;           // [N][blocks per frame][2]  (min/max partials written by reproject)
     int* blk_offsets = nullptr;
     int* rs_x = nullptr;                      // resize tables: x0 x1 a0 a1 [w], y0 y1 b0 b1 [h]
     int* rs_y = nullptr;
@@ -82,7 +86,8 @@ struct sa_handle {
     // state
     const uint8_t* color_src[2] = {nullptr, nullptr};  // what reproject takes colours from / copy_rectified returns
     size_t color_pitch = 0, color_frame = 0;
-    int minmax_valid = 0;  // number of frames whose min/max is current
+    int minmax_valid = 0;  // number of frames whose final min/max is current
+    int partial_valid = 0; // number of frames whose per-CTA min/max partials are current
     int n_last = 0;
     sa_engine_fn engine = nullptr;
     void* engine_user = nullptr;
@@ -91,6 +96,8 @@ struct sa_handle {
     long opt_frame_fastest = 1;
     long opt_chunk = 8;
     long opt_force_direct = 0;
+    long opt_force_generic = 0;
+    long opt_exact_div = 0;
 
     long launches = 0;
     sa::StageTimer timer;
@@ -142,6 +149,7 @@ struct RectifyArgs {
     int model, dtype;
     int write_tensor;                  // 0 when a resize follows
     int frame_fastest;
+    int force_generic;                 // testing: never take the fast tile path
 };
 cudaError_t launch_rectify(const RectifyArgs& a, cudaStream_t s, long* launches);
 
@@ -174,13 +182,15 @@ struct ReprojectArgs {
     int w, h, n;
     int negate;               // RAFTStereo
     int compact;
-    unsigned* minmax;         // [n][2], may be null
+    int exact_div;            // 1: IEEE divisions (bit-identical to the reference arithmetic), 0: shared-reciprocal quotients
+    unsigned* blk_minmax;     // scratch [n][nblk][2]: per-CTA (min, ~max) of the disparity as used; may be null
     int* blk_counts;          // scratch [n][nblk]
     int* blk_offsets;         // scratch [n][nblk]
     int* counts;              // [n] device
 };
 cudaError_t launch_reproject(const ReprojectArgs& a, cudaStream_t s, long* launches);
 int reproject_blocks_per_frame(int w, int h);
+cudaError_t launch_reduce_minmax(const unsigned* blk_minmax, int nblk, int n, unsigned* minmax, cudaStream_t s, long* launches);
 
 cudaError_t launch_minmax(const float* disp, size_t disp_frame, int npix, int n, unsigned* minmax, cudaStream_t s, long* launches);
 cudaError_t launch_heatmap(const float* disp, size_t disp_frame, int npix, int n, const unsigned* minmax, uint8_t* out, cudaStream_t s, long* launches);

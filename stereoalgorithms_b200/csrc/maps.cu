@@ -92,7 +92,13 @@ __global__ void __launch_bounds__(256) tile_info_kernel(const int* __restrict__ 
         int w = ((xmax + 2 - x0) + 3) & ~3;      // taps reach sx+1
         int h = ymax + 2 - ymin;
         t.x0 = (short)x0; t.y0 = (short)ymin; t.w = (short)w; t.h = (short)h;
+        t.inv_gw = 0; t.flags = 0;
         if (force_direct || w * h > kFootprintWords || w <= 0 || h <= 0) { t.w = 0; t.h = 0; }
+        else {
+            const uint32_t gw = (uint32_t)w >> 2;
+            t.inv_gw = ((1u << 20) + gw - 1) / gw;
+            if (x0 >= 0 && ymin >= 0 && x0 + w <= W && ymin + h <= H) t.flags |= kTileInterior;
+        }
         tiles[tile] = t;
     }
 }

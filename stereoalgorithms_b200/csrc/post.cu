@@ -32,13 +32,15 @@ __global__ void __launch_bounds__(256) minmax_kernel(const float* __restrict__ d
         const float v = d[i];
         mn = fminf(mn, v); mx = fmaxf(mx, v);
     }
-    for (int o = 16; o; o >>= 1) {
-        mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
-        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-    }
-    if ((threadIdx.x & 31) == 0) {
-        atomicMin(minmax + 2 * frame, enc_ordered(mn));
-        atomicMin(minmax + 2 * frame + 1, ~enc_ordered(mx));
+    __shared__ unsigned s_mm[16];
+    const unsigned a = __reduce_min_sync(0xffffffffu, enc_ordered(mn)), b = __reduce_min_sync(0xffffffffu, ~enc_ordered(mx));
+    if ((threadIdx.x & 31) == 0) { s_mm[2 * (threadIdx.x >> 5)] = a; s_mm[2 * (threadIdx.x >> 5) + 1] = b; }
+    __syncthreads();
+    if (threadIdx.x == 0) {      // one atomic pair per CTA (a few dozen per frame)
+        unsigned x = s_mm[0], y = s_mm[1];
+        for (int i = 1; i < 8; i++) { x = min(x, s_mm[2 * i]); y = min(y, s_mm[2 * i + 1]); }
+        atomicMin(minmax + 2 * frame, x);
+        atomicMin(minmax + 2 * frame + 1, y);
     }
 }
 

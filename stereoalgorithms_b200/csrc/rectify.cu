@@ -14,7 +14,8 @@
 //      evaluated as ((top*(32-fy) + bot*fy + 512) >> 10), which is the same integer because nothing is rounded
 //      in between; B and R share one 32-bit multiply (two 16-bit lanes);
 //   4. the normalised RGB planes go straight to global memory (a warp writes 32 consecutive floats/halves of a
-//      plane row), the rectified BGR bytes go through shared memory and leave as 16-byte row segments.
+//      plane row); the rectified BGR bytes of four neighbouring lanes are packed into three words with one
+//      shuffle + byte-permute and leave as 96-byte coalesced row segments (edge tiles: through shared memory).
 #include "common.h"
 
 namespace sa {
@@ -53,90 +54,180 @@ struct TensorT { using type = float; };
 template <>
 struct TensorT<SA_F16> { using type = __half; };
 
-template <int DTYPE, bool IDENT, bool WRITE_TENSOR, bool ALIGNED4>
-__global__ void __launch_bounds__(kRectThreads, 6) rectify_kernel(const RectifyArgs a, int tiles_x, int tiles_per_frame, int out_align)
+// OpenCV's fixed-point bilinear blend of one output pixel from its four BGRx taps.
+//   (p00*w00 + p01*w01 + p10*w10 + p11*w11 + 2^14) >> 15  with  w = (32-fx|fx)*(32-fy|fy)*32
+// == ((top*(32-fy) + bot*fy + 512) >> 10)  with  top/bot = p_left*(32-fx) + p_right*fx   (nothing rounded in between).
+// B and R travel in the two 16-bit lanes of one word through the horizontal pass (each lane <= 255*32).
+__device__ __forceinline__ void blend(uint32_t p00, uint32_t p01, uint32_t p10, uint32_t p11, uint32_t fx, uint32_t fy, uint32_t& vB, uint32_t& vG,
+                                      uint32_t& vR)
 {
-    using T = typename TensorT<DTYPE>::type;
-    __shared__ __align__(16) uint32_t s_src[kFootprintWords];
-    __shared__ __align__(16) uint32_t s_out[kTileH * kTileW * 3 / 4];
-    __shared__ T s_lut[IDENT ? 1 : 768];
+    const uint32_t ax = 32u - fx, ay = 32u - fy;
+    const uint32_t tBR = (p00 & 0x00ff00ffu) * ax + (p01 & 0x00ff00ffu) * fx;
+    const uint32_t bBR = (p10 & 0x00ff00ffu) * ax + (p11 & 0x00ff00ffu) * fx;
+    const uint32_t tG = __byte_perm(p00, 0, 0x4441) * ax + __byte_perm(p01, 0, 0x4441) * fx;
+    const uint32_t bG = __byte_perm(p10, 0, 0x4441) * ax + __byte_perm(p11, 0, 0x4441) * fx;
+    vB = ((tBR & 0xffffu) * ay + (bBR & 0xffffu) * fy + 512u) >> 10;
+    vR = ((tBR >> 16) * ay + (bBR >> 16) * fy + 512u) >> 10;
+    vG = (tG * ay + bG * fy + 512u) >> 10;
+}
 
-    const int tid = threadIdx.x;
-    int tile, fe;
-    if (a.frame_fastest) { fe = blockIdx.x % (2 * a.n); tile = blockIdx.x / (2 * a.n); }
-    else { tile = blockIdx.x % tiles_per_frame; fe = blockIdx.x / tiles_per_frame; }
-    const int eye = fe & 1, frame = fe >> 1;
-    const int W = a.W, H = a.H;
-    const int tyi = tile / tiles_x;
-    const int tx0 = (tile - tyi * tiles_x) * kTileW, ty0 = tyi * kTileH;
-
-    const uint8_t* __restrict__ src = a.src[eye] + (size_t)frame * a.src_frame;
-    const size_t pitch = a.src_pitch;
-    const TileInfo ti = a.tiles[eye][tile];
-
-    if (!IDENT) {
-        const T* lut = static_cast<const T*>(a.lut);
-        for (int i = tid; i < 768; i += kRectThreads) s_lut[i] = lut[i];
+template <int DTYPE, bool IDENT, typename T>
+__device__ __forceinline__ void normalise(const T* s_lut, uint32_t vB, uint32_t vG, uint32_t vR, T& r, T& g, T& b)
+{
+    if (IDENT) {
+        if (DTYPE == SA_F16) { r = (T)__ushort2half_rn((unsigned short)vR); g = (T)__ushort2half_rn((unsigned short)vG); b = (T)__ushort2half_rn((unsigned short)vB); }
+        else {  // (float)v for v < 2^23 without the conversion unit: 2^23 + v, exactly, minus 2^23
+            r = (T)(__uint_as_float(0x4b000000u | vR) - 8388608.0f);
+            g = (T)(__uint_as_float(0x4b000000u | vG) - 8388608.0f);
+            b = (T)(__uint_as_float(0x4b000000u | vB) - 8388608.0f);
+        }
+    } else {
+        r = s_lut[vR]; g = s_lut[256 + vG]; b = s_lut[512 + vB];
     }
+}
 
-    // ---- 1. map entries of this thread's pixels -------------------------------------------------
-    const int lx = tid & (kTileW - 1), ly0 = tid >> 6;
-    const int x = tx0 + lx;
-    int m1[4];
-    uint32_t m2[4];
-    const int* __restrict__ map1 = a.map1[eye];
-    const uint16_t* __restrict__ map2 = a.map2[eye];
-#pragma unroll
-    for (int k = 0; k < 4; k++) {
-        const int y = ty0 + ly0 + 4 * k;
-        m1[k] = 0; m2[k] = 0;
-        if (x < W && y < H) {
-            const size_t o = (size_t)y * W + x;
-            m1[k] = __ldg(map1 + o);
-            m2[k] = __ldg(map2 + o);
+// Stage a footprint row group (4 source pixels, 12 bytes -> four BGRx words) with per-pixel bounds checks.
+template <bool ALIGNED4>
+__device__ __forceinline__ uint4 stage_checked(const uint8_t* __restrict__ src, size_t pitch, int W, int H, int xx, int yy)
+{
+    uint4 o = make_uint4(0u, 0u, 0u, 0u);
+    if ((unsigned)yy < (unsigned)H) {
+        if (ALIGNED4 && xx >= 0 && xx + 3 < W) {
+            const uint32_t* p = reinterpret_cast<const uint32_t*>(src + (size_t)yy * pitch + 3 * xx);
+            const uint32_t u0 = __ldg(p), u1 = __ldg(p + 1), u2 = __ldg(p + 2);
+            o.x = u0;  // byte 3 of a staged word is never read
+            o.y = __byte_perm(u0, u1, 0x4543);
+            o.z = __byte_perm(u1, u2, 0x4432);
+            o.w = u2 >> 8;
+        } else {
+            o.x = fetch_px(src, pitch, W, H, xx, yy);
+            o.y = fetch_px(src, pitch, W, H, xx + 1, yy);
+            o.z = fetch_px(src, pitch, W, H, xx + 2, yy);
+            o.w = fetch_px(src, pitch, W, H, xx + 3, yy);
         }
     }
+    return o;
+}
 
-    // ---- 2. stage the source footprint --------------------------------------------------------
+// ---- fast path: a full 64x16 tile, staged footprint, 4-byte aligned rectified rows ----------------------------
+// No bounds tests on the output side, 32-bit offsets, and the rectified BGR bytes leave straight from registers:
+// lanes 4j..4j+3 hold 4 consecutive pixels = 12 bytes = 3 words; one shuffle + one byte-permute per lane builds
+// word m in lane 4j+m (m < 3), so a warp row segment (32 pixels) is one 96-byte coalesced store.
+template <int DTYPE, bool IDENT, bool WRITE_TENSOR, bool ALIGNED4>
+__device__ __forceinline__ void tile_fast(const RectifyArgs& a, const TileInfo ti, int eye, int frame, int tx0, int ty0, uint32_t* s_src,
+                                          const typename TensorT<DTYPE>::type* s_lut)
+{
+    using T = typename TensorT<DTYPE>::type;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int W = a.W, H = a.H;
+    const int lx = tid & (kTileW - 1), ly0 = tid >> 6;
+    const int pix0 = (ty0 + ly0) * W + tx0 + lx;
+    const int rstep = 4 * W;
+
+    const int* __restrict__ map1 = eye ? a.map1[1] : a.map1[0];
+    const uint16_t* __restrict__ map2 = eye ? a.map2[1] : a.map2[0];
+    int m1[4];
+    uint32_t m2[4];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        m1[k] = __ldg(map1 + pix0 + k * rstep);
+        m2[k] = __ldg(map2 + pix0 + k * rstep);
+    }
+
+    const uint8_t* __restrict__ src = (eye ? a.src[1] : a.src[0]) + (size_t)frame * a.src_frame;
     const int fw = ti.w, X0 = ti.x0, Y0 = ti.y0;
-    const bool staged = fw > 0;
-    if (staged) {
+    {
         const int gw = fw >> 2, total = gw * ti.h;
-        for (int g = tid; g < total; g += kRectThreads) {
-            const int r = g / gw, c4 = (g - r * gw) << 2;
-            const int yy = Y0 + r, xx = X0 + c4;
-            uint4 o = make_uint4(0u, 0u, 0u, 0u);
-            if ((unsigned)yy < (unsigned)H) {
-                const uint8_t* rowp = src + (size_t)yy * pitch;
-                if (ALIGNED4 && xx >= 0 && xx + 3 < W) {
-                    const uint32_t* p = reinterpret_cast<const uint32_t*>(rowp + 3 * xx);
-                    const uint32_t u0 = __ldg(p), u1 = __ldg(p + 1), u2 = __ldg(p + 2);
-                    o.x = u0;  // byte 3 of a staged word is never read
-                    o.y = __byte_perm(u0, u1, 0x4543);
-                    o.z = __byte_perm(u1, u2, 0x4432);
-                    o.w = u2 >> 8;
-                } else {
-                    o.x = fetch_px(src, pitch, W, H, xx, yy);
-                    o.y = fetch_px(src, pitch, W, H, xx + 1, yy);
-                    o.z = fetch_px(src, pitch, W, H, xx + 2, yy);
-                    o.w = fetch_px(src, pitch, W, H, xx + 3, yy);
-                }
+        const uint32_t inv = ti.inv_gw;                        // ceil(2^20 / gw): g / gw == (g * inv) >> 20 for g < 768
+        if (ALIGNED4 && (ti.flags & kTileInterior)) {
+            const int pitch = (int)a.src_pitch;
+            const uint8_t* base = src + Y0 * pitch + 3 * X0;   // frame < 2 GB (checked on the host)
+            for (int g = tid; g < total; g += kRectThreads) {
+                const int r = (int)(((uint32_t)g * inv) >> 20), c = g - r * gw;
+                const uint32_t* p = reinterpret_cast<const uint32_t*>(base + r * pitch + 12 * c);
+                const uint32_t u0 = __ldg(p), u1 = __ldg(p + 1), u2 = __ldg(p + 2);
+                uint4 o;
+                o.x = u0;
+                o.y = __byte_perm(u0, u1, 0x4543);
+                o.z = __byte_perm(u1, u2, 0x4432);
+                o.w = u2 >> 8;
+                *reinterpret_cast<uint4*>(&s_src[g << 2]) = o;   // row stride == fw words, so word index = 4*g
             }
-            *reinterpret_cast<uint4*>(&s_src[r * fw + c4]) = o;
+        } else {
+            for (int g = tid; g < total; g += kRectThreads) {
+                const int r = (int)(((uint32_t)g * inv) >> 20), c4 = (g - r * gw) << 2;
+                *reinterpret_cast<uint4*>(&s_src[g << 2]) = stage_checked<ALIGNED4>(src, a.src_pitch, W, H, X0 + c4, Y0 + r);
+            }
         }
     }
     __syncthreads();
 
-    // ---- 3. blend, normalise, store ------------------------------------------------------------
+    const int plane = W * H;
+    T* __restrict__ tb = WRITE_TENSOR ? static_cast<T*>(eye ? a.tensor[1] : a.tensor[0]) + (size_t)frame * a.tensor_frame : nullptr;
+    uint32_t* __restrict__ rect32 = reinterpret_cast<uint32_t*>((eye ? a.rect[1] : a.rect[0]) + (size_t)frame * plane * 3);
+    const int m = lane & 3;
+    const uint32_t sel = m == 0 ? 0x4210u : (m == 1 ? 0x5421u : 0x6542u);
+    const int wbase = 3 * ((pix0 - m) >> 2) + m, wstep = 3 * W;
+    const int soff = -Y0 * fw - X0;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        int sx = (int)(short)(m1[k] & 0xffff), sy = m1[k] >> 16;
+        sx = max(-2, min(W, sx));
+        sy = max(-2, min(H, sy));
+        const uint32_t* p = s_src + (sy * fw + sx + soff);
+        uint32_t vB, vG, vR;
+        blend(p[0], p[1], p[fw], p[fw + 1], m2[k] & 31u, (m2[k] >> 5) & 31u, vB, vG, vR);
+        const uint32_t v = vB | (vG << 8) | (vR << 16);
+        const uint32_t nb = __shfl_down_sync(0xffffffffu, v, 1);
+        if (m < 3) rect32[wbase + k * wstep] = __byte_perm(v, nb, sel);
+        if (WRITE_TENSOR) {
+            T r, g, b;
+            normalise<DTYPE, IDENT, T>(s_lut, vB, vG, vR, r, g, b);
+            const int o = pix0 + k * rstep;
+            tb[o] = r; tb[o + plane] = g; tb[o + 2 * plane] = b;
+        }
+    }
+}
+
+// ---- generic path: partial tiles at the right/bottom edge, footprints too large to stage, odd alignments ---------
+template <int DTYPE, bool IDENT, bool WRITE_TENSOR, bool ALIGNED4>
+__device__ __forceinline__ void tile_generic(const RectifyArgs& a, const TileInfo ti, int eye, int frame, int tx0, int ty0, int out_align,
+                                             uint32_t* s_src, uint32_t* s_out, const typename TensorT<DTYPE>::type* s_lut)
+{
+    using T = typename TensorT<DTYPE>::type;
+    const int tid = threadIdx.x;
+    const int W = a.W, H = a.H;
+    const uint8_t* __restrict__ src = (eye ? a.src[1] : a.src[0]) + (size_t)frame * a.src_frame;
+    const size_t pitch = a.src_pitch;
+
+    const int lx = tid & (kTileW - 1), ly0 = tid >> 6;
+    const int x = tx0 + lx;
+    const int* __restrict__ map1 = eye ? a.map1[1] : a.map1[0];
+    const uint16_t* __restrict__ map2 = eye ? a.map2[1] : a.map2[0];
+
+    const int fw = ti.w, X0 = ti.x0, Y0 = ti.y0;
+    const bool staged = fw > 0;
+    if (staged) {
+        const int gw = fw >> 2, total = gw * ti.h;
+        const uint32_t inv = ti.inv_gw;
+        for (int g = tid; g < total; g += kRectThreads) {
+            const int r = (int)(((uint32_t)g * inv) >> 20), c4 = (g - r * gw) << 2;
+            *reinterpret_cast<uint4*>(&s_src[g << 2]) = stage_checked<ALIGNED4>(src, pitch, W, H, X0 + c4, Y0 + r);
+        }
+    }
+    __syncthreads();
+
     uint8_t* s_out_b = reinterpret_cast<uint8_t*>(s_out);
     const size_t plane = (size_t)W * H;
-    T* __restrict__ tbase = WRITE_TENSOR ? static_cast<T*>(a.tensor[eye]) + (size_t)frame * a.tensor_frame : nullptr;
-#pragma unroll
+    T* __restrict__ tbase = WRITE_TENSOR ? static_cast<T*>(eye ? a.tensor[1] : a.tensor[0]) + (size_t)frame * a.tensor_frame : nullptr;
+#pragma unroll 1
     for (int k = 0; k < 4; k++) {
         const int ly = ly0 + 4 * k, y = ty0 + ly;
         if (x < W && y < H) {
-            int sx = (int)(short)(m1[k] & 0xffff), sy = m1[k] >> 16;
-            const uint32_t fx = m2[k] & 31u, fy = (m2[k] >> 5) & 31u;
+            const size_t mo = (size_t)y * W + x;
+            const int m1 = __ldg(map1 + mo);
+            const uint32_t m2 = __ldg(map2 + mo);
+            int sx = (int)(short)(m1 & 0xffff), sy = m1 >> 16;
             uint32_t p00, p01, p10, p11;
             if (staged) {
                 sx = max(-2, min(W, sx));
@@ -149,43 +240,53 @@ __global__ void __launch_bounds__(kRectThreads, 6) rectify_kernel(const RectifyA
                 p10 = fetch_px(src, pitch, W, H, sx, sy + 1);
                 p11 = fetch_px(src, pitch, W, H, sx + 1, sy + 1);
             }
-            const uint32_t ax = 32u - fx, ay = 32u - fy;
-            // horizontal pass: B and R in the two 16-bit lanes of one word (<= 255*32 each), G alone
-            const uint32_t tBR = (p00 & 0x00ff00ffu) * ax + (p01 & 0x00ff00ffu) * fx;
-            const uint32_t bBR = (p10 & 0x00ff00ffu) * ax + (p11 & 0x00ff00ffu) * fx;
-            const uint32_t tG = ((p00 >> 8) & 0xffu) * ax + ((p01 >> 8) & 0xffu) * fx;
-            const uint32_t bG = ((p10 >> 8) & 0xffu) * ax + ((p11 >> 8) & 0xffu) * fx;
-            // vertical pass + rounding: (sum*32 + 2^14) >> 15 == (sum + 512) >> 10
-            const uint32_t vB = ((tBR & 0xffffu) * ay + (bBR & 0xffffu) * fy + 512u) >> 10;
-            const uint32_t vR = ((tBR >> 16) * ay + (bBR >> 16) * fy + 512u) >> 10;
-            const uint32_t vG = (tG * ay + bG * fy + 512u) >> 10;
-
+            uint32_t vB, vG, vR;
+            blend(p00, p01, p10, p11, m2 & 31u, (m2 >> 5) & 31u, vB, vG, vR);
             uint8_t* so = s_out_b + (ly * kTileW + lx) * 3;
             so[0] = (uint8_t)vB; so[1] = (uint8_t)vG; so[2] = (uint8_t)vR;
-
             if (WRITE_TENSOR) {
                 T* t = tbase + (size_t)y * W + x;
                 T r, g, b;
-                if (IDENT) {
-                    if (DTYPE == SA_F16) { r = (T)__ushort2half_rn((unsigned short)vR); g = (T)__ushort2half_rn((unsigned short)vG); b = (T)__ushort2half_rn((unsigned short)vB); }
-                    else { r = (T)(float)vR; g = (T)(float)vG; b = (T)(float)vB; }
-                } else {
-                    r = s_lut[vR]; g = s_lut[256 + vG]; b = s_lut[512 + vB];
-                }
+                normalise<DTYPE, IDENT, T>(s_lut, vB, vG, vR, r, g, b);
                 t[0] = r; t[plane] = g; t[2 * plane] = b;
             }
         }
     }
     __syncthreads();
 
-    // ---- 4. rectified BGR tile -> global, widest stores the alignment allows ---------------------
+    // rectified BGR tile -> global, widest stores the alignment allows
     const int rows = min(kTileH, H - ty0), row_bytes = min(kTileW, W - tx0) * 3;
-    uint8_t* g = a.rect[eye] + (size_t)frame * plane * 3 + ((size_t)ty0 * W + tx0) * 3;
+    uint8_t* g = (eye ? a.rect[1] : a.rect[0]) + (size_t)frame * plane * 3 + ((size_t)ty0 * W + tx0) * 3;
     const size_t gpitch = (size_t)W * 3;
     if (out_align >= 16) copy_rows<uint4>(g, gpitch, s_out_b, rows, row_bytes);
     else if (out_align >= 4) copy_rows<uint32_t>(g, gpitch, s_out_b, rows, row_bytes);
     else if (out_align >= 2) copy_rows<uint16_t>(g, gpitch, s_out_b, rows, row_bytes);
     else copy_rows<uint8_t>(g, gpitch, s_out_b, rows, row_bytes);
+}
+
+// grid: frame_fastest ? (2n, tiles_x, tiles_y) : (tiles_x, tiles_y, 2n)   [eye = fe & 1, frame = fe >> 1]
+template <int DTYPE, bool IDENT, bool WRITE_TENSOR, bool ALIGNED4>
+__global__ void __launch_bounds__(kRectThreads, 6) rectify_kernel(const RectifyArgs a, int tiles_x, int out_align, int fast_ok)
+{
+    using T = typename TensorT<DTYPE>::type;
+    __shared__ __align__(16) uint32_t s_src[kFootprintWords];
+    __shared__ __align__(16) uint32_t s_out[kTileH * kTileW * 3 / 4];
+    __shared__ T s_lut[IDENT ? 1 : 768];
+
+    int txi, tyi, fe;
+    if (a.frame_fastest) { fe = blockIdx.x; txi = blockIdx.y; tyi = blockIdx.z; }
+    else { txi = blockIdx.x; tyi = blockIdx.y; fe = blockIdx.z; }
+    const int eye = fe & 1, frame = fe >> 1;
+    const int tx0 = txi * kTileW, ty0 = tyi * kTileH;
+    const TileInfo ti = (eye ? a.tiles[1] : a.tiles[0])[tyi * tiles_x + txi];
+
+    if (!IDENT) {
+        const T* lut = static_cast<const T*>(a.lut);
+        for (int i = threadIdx.x; i < 768; i += kRectThreads) s_lut[i] = lut[i];
+    }
+    const bool full = tx0 + kTileW <= a.W && ty0 + kTileH <= a.H;
+    if (fast_ok && full && ti.w > 0) tile_fast<DTYPE, IDENT, WRITE_TENSOR, ALIGNED4>(a, ti, eye, frame, tx0, ty0, s_src, s_lut);
+    else tile_generic<DTYPE, IDENT, WRITE_TENSOR, ALIGNED4>(a, ti, eye, frame, tx0, ty0, out_align, s_src, s_out, s_lut);
 }
 
 // rectify = 0 (images already rectified) and the tail of the resize path: BGR u8 -> normalised planes only.
@@ -220,10 +321,10 @@ __global__ void __launch_bounds__(256) preprocess_kernel(const PreprocArgs a)
 inline bool lut_is_identity(int model) { return model == SA_MODEL_RAFTSTEREO || model == SA_MODEL_CRESTEREO; }
 
 template <int DTYPE, bool IDENT, bool WT>
-cudaError_t launch_rectify_t(const RectifyArgs& a, bool aligned4, int tiles_x, int tpf, int out_align, unsigned grid, cudaStream_t s)
+cudaError_t launch_rectify_t(const RectifyArgs& a, bool aligned4, int tiles_x, int out_align, int fast_ok, dim3 grid, cudaStream_t s)
 {
-    if (aligned4) rectify_kernel<DTYPE, IDENT, WT, true><<<grid, kRectThreads, 0, s>>>(a, tiles_x, tpf, out_align);
-    else rectify_kernel<DTYPE, IDENT, WT, false><<<grid, kRectThreads, 0, s>>>(a, tiles_x, tpf, out_align);
+    if (aligned4) rectify_kernel<DTYPE, IDENT, WT, true><<<grid, kRectThreads, 0, s>>>(a, tiles_x, out_align, fast_ok);
+    else rectify_kernel<DTYPE, IDENT, WT, false><<<grid, kRectThreads, 0, s>>>(a, tiles_x, out_align, fast_ok);
     return cudaGetLastError();
 }
 
@@ -239,15 +340,19 @@ cudaError_t launch_rectify(const RectifyArgs& a, cudaStream_t s, long* launches)
 {
     if (a.n <= 0) return cudaSuccess;
     const int tiles_x = (a.W + kTileW - 1) / kTileW, tiles_y = (a.H + kTileH - 1) / kTileH;
-    const int tpf = tiles_x * tiles_y;
-    const unsigned grid = (unsigned)tpf * 2u * (unsigned)a.n;
+    if (tiles_x > 65535 || tiles_y > 65535 || 2 * a.n > 65535) return cudaErrorInvalidConfiguration;
+    const dim3 grid = a.frame_fastest ? dim3(2u * (unsigned)a.n, (unsigned)tiles_x, (unsigned)tiles_y)
+                                      : dim3((unsigned)tiles_x, (unsigned)tiles_y, 2u * (unsigned)a.n);
     // input alignment: every row of every frame of both eyes starts on a 4-byte boundary
     const bool aligned4 = min3(ptr_align(a.src[0]), ptr_align(a.src[1]), min3(size_align(a.src_pitch), size_align(a.src_frame), 256)) >= 4;
     // output alignment of the rectified rows (tile x offsets are multiples of 192 bytes)
     const int out_align = min3(ptr_align(a.rect[0]), ptr_align(a.rect[1]), min3(size_align((size_t)a.W * 3), size_align((size_t)a.W * a.H * 3), 256));
+    // fast path: 4-byte aligned rectified rows and 32-bit offsets inside a frame
+    const int fast_ok = (out_align >= 4 && a.W % 4 == 0 && a.src_pitch * (size_t)a.H < (1u << 31) && (size_t)a.W * a.H * 3 < (1u << 30) &&
+                         !a.force_generic) ? 1 : 0;
     const bool ident = lut_is_identity(a.model);
     cudaError_t e;
-#define SA_RECT(DT, ID, WT) e = launch_rectify_t<DT, ID, WT>(a, aligned4, tiles_x, tpf, out_align, grid, s)
+#define SA_RECT(DT, ID, WT) e = launch_rectify_t<DT, ID, WT>(a, aligned4, tiles_x, out_align, fast_ok, grid, s)
     if (!a.write_tensor) SA_RECT(SA_F32, true, false);
     else if (a.dtype == SA_F16) { if (ident) SA_RECT(SA_F16, true, true); else SA_RECT(SA_F16, false, true); }
     else { if (ident) SA_RECT(SA_F32, true, true); else SA_RECT(SA_F32, false, true); }

