@@ -108,7 +108,7 @@ static int compute_maps(sa_handle* h)
         {
             StageScope t(h, SA_STAGE_MAPS, h->stream);
             SA_CUDA(h, launch_init_maps(p, h->W, h->H, h->map1[eye], h->map2[eye], h->stream));
-            SA_CUDA(h, launch_tile_info(h->map1[eye], h->W, h->H, h->tiles[eye], tiles_x(h), tiles_y(h), (int)h->opt_force_direct, h->stream));
+            SA_CUDA(h, launch_tile_info(h->map1[eye], h->map2[eye], h->W, h->H, h->tiles[eye], h->tmap[eye], tiles_x(h), tiles_y(h), (int)h->opt_force_direct, h->stream));
             h->launches += 2;
         }
         h->have_maps[eye] = true;
@@ -173,13 +173,14 @@ static int stage_rectify(sa_handle* h, int f0, int n, const uint8_t* src_l, cons
         a.src[0] = src_l; a.src[1] = src_r;
         a.rect[0] = h->rect[0] + (size_t)f0 * rect_frame; a.rect[1] = h->rect[1] + (size_t)f0 * rect_frame;
         a.tensor[0] = t_l; a.tensor[1] = t_r;
-        for (int e = 0; e < 2; e++) { a.map1[e] = h->map1[e]; a.map2[e] = h->map2[e]; a.tiles[e] = h->tiles[e]; }
+        for (int e = 0; e < 2; e++) { a.map1[e] = h->map1[e]; a.map2[e] = h->map2[e]; a.tiles[e] = h->tiles[e]; a.tmap[e] = h->tmap[e]; }
         a.lut = lut;
         a.src_pitch = pitch; a.src_frame = frame_bytes; a.tensor_frame = tframe;
         a.W = h->W; a.H = h->H; a.n = n; a.model = h->cfg.model; a.dtype = h->cfg.tensor_dtype;
         a.write_tensor = h->resize ? 0 : 1;
         a.frame_fastest = (int)h->opt_frame_fastest;
         a.force_generic = (int)h->opt_force_generic;
+        a.persistent_ctas = (int)(h->opt_persistent > 0 ? h->opt_persistent * h->sm_count : 0);
         {
             StageScope t(h, SA_STAGE_RECTIFY, s);
             SA_CUDA(h, launch_rectify(a, s, &h->launches));
@@ -311,6 +312,7 @@ int sa_create(const sa_config* cfg, sa_handle** out)
     h->planes = cfg->model == SA_MODEL_CRESTEREO ? 2 : 1;
     h->max_n = cfg->max_batch;
     h->tensor_elt = cfg->tensor_dtype == SA_F16 ? 2 : 4;
+    { int sms = 0; if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, cfg->gpu_id) == cudaSuccess && sms > 0) h->sm_count = sms; }
 
     const size_t N = (size_t)h->max_n, img = (size_t)h->W * h->H * 3, npix = (size_t)h->w * h->h, mpix = (size_t)h->W * h->H;
     const int ntiles = tiles_x(h) * tiles_y(h);
@@ -327,6 +329,7 @@ int sa_create(const sa_config* cfg, sa_handle** out)
         A(dev_alloc(&h->map1[eye], mpix));
         A(dev_alloc(&h->map2[eye], mpix));
         A(dev_alloc(&h->tiles[eye], (size_t)ntiles));
+        A(dev_alloc(&h->tmap[eye], mpix));
     }
     if (ok) {
         // one allocation for both eyes' tensors: [left N x 3 planes][right N x 3 planes], HitNet: N x 6 planes interleaved per frame
@@ -382,7 +385,7 @@ int sa_destroy(sa_handle* h)
     if (h->s_h2d) cudaStreamSynchronize(h->s_h2d);
     if (h->s_d2h) cudaStreamSynchronize(h->s_d2h);
     for (int e = 0; e < 2; e++) {
-        cudaFree(h->raw[e]); cudaFree(h->rect[e]); cudaFree(h->net_u8[e]); cudaFree(h->map1[e]); cudaFree(h->map2[e]); cudaFree(h->tiles[e]);
+        cudaFree(h->raw[e]); cudaFree(h->rect[e]); cudaFree(h->net_u8[e]); cudaFree(h->map1[e]); cudaFree(h->map2[e]); cudaFree(h->tiles[e]); cudaFree(h->tmap[e]);
     }
     cudaFree(h->tensor[0]); cudaFree(h->disp); cudaFree(h->points); cudaFree(h->heat); cudaFree(h->counts); cudaFree(h->minmax);
     cudaFree(h->blk_counts); cudaFree(h->blk_offsets); cudaFree(h->blk_minmax); cudaFree(h->lut32); cudaFree(h->lut16); cudaFree(h->rs_x); cudaFree(h->rs_y);
@@ -508,7 +511,7 @@ int sa_set_maps(sa_handle* h, int eye, const int16_t* map1, const uint16_t* map2
     const size_t mpix = (size_t)h->W * h->H;
     SA_CUDA(h, cudaMemcpyAsync(h->map1[eye], map1, mpix * 4, cudaMemcpyHostToDevice, h->stream));
     SA_CUDA(h, cudaMemcpyAsync(h->map2[eye], map2, mpix * 2, cudaMemcpyHostToDevice, h->stream));
-    SA_CUDA(h, launch_tile_info(h->map1[eye], h->W, h->H, h->tiles[eye], tiles_x(h), tiles_y(h), (int)h->opt_force_direct, h->stream));
+    SA_CUDA(h, launch_tile_info(h->map1[eye], h->map2[eye], h->W, h->H, h->tiles[eye], h->tmap[eye], tiles_x(h), tiles_y(h), (int)h->opt_force_direct, h->stream));
     h->launches += 1;
     SA_CUDA(h, cudaStreamSynchronize(h->stream));
     h->have_maps[eye] = true;
@@ -823,6 +826,7 @@ int sa_set_option(sa_handle* h, const char* key, long value)
     else if (!std::strcmp(key, "force_direct")) h->opt_force_direct = value;   // takes effect at the next map computation
     else if (!std::strcmp(key, "force_generic")) h->opt_force_generic = value;
     else if (!std::strcmp(key, "exact_div")) h->opt_exact_div = value;
+    else if (!std::strcmp(key, "persistent")) h->opt_persistent = value;
     else return fail(h, SA_ERR_INVALID_ARG, "sa_set_option: unknown key '%s'", key);
     return SA_OK;
 }

@@ -74,6 +74,7 @@ struct sa_handle {
     int* map1[2] = {nullptr, nullptr};        // (x | y << 16) int16 pairs, [H][W]
     uint16_t* map2[2] = {nullptr, nullptr};
     sa::TileInfo* tiles[2] = {nullptr, nullptr};
+    uint32_t* tmap[2] = {nullptr, nullptr};   // derived per-pixel table of the fast rectify path, [H][W]
     float* lut32 = nullptr;                   // [3][256]
     __half* lut16 = nullptr;
     unsigned* minmax = nullptr;               // [N][2] ordered-uint encodings (min, ~max)
@@ -98,6 +99,8 @@ struct sa_handle {
     long opt_force_direct = 0;
     long opt_force_generic = 0;
     long opt_exact_div = 0;
+    long opt_persistent = 0;          // CTAs per SM of the persistent rectify kernel (0 = one CTA per tile, the default: measured faster)
+    int sm_count = 148;
 
     long launches = 0;
     sa::StageTimer timer;
@@ -133,7 +136,8 @@ int parse_opencv_yaml(const char* path, std::vector<YamlMat>& out, std::string& 
 
 // kernels (each returns a cudaError_t from the launch)
 cudaError_t launch_init_maps(const MapParams& p, int W, int H, int* map1, uint16_t* map2, cudaStream_t s);
-cudaError_t launch_tile_info(const int* map1, int W, int H, TileInfo* tiles, int tiles_x, int tiles_y, int force_direct, cudaStream_t s);
+cudaError_t launch_tile_info(const int* map1, const uint16_t* map2, int W, int H, TileInfo* tiles, uint32_t* tmap, int tiles_x, int tiles_y, int force_direct,
+                             cudaStream_t s);
 
 struct RectifyArgs {
     const uint8_t* src[2];
@@ -142,6 +146,7 @@ struct RectifyArgs {
     const int* map1[2];
     const uint16_t* map2[2];
     const TileInfo* tiles[2];
+    const uint32_t* tmap[2];  // per pixel: staged-footprint word offset | fx << 12 | fy << 17 (0xffffffff in unstaged tiles)
     const void* lut;          // float[3][256] or __half[3][256]
     size_t src_pitch, src_frame;       // bytes
     size_t tensor_frame;               // elements between consecutive frames of one eye
@@ -150,6 +155,7 @@ struct RectifyArgs {
     int write_tensor;                  // 0 when a resize follows
     int frame_fastest;
     int force_generic;                 // testing: never take the fast tile path
+    int persistent_ctas;               // > 0: persistent pipelined kernel with this many CTAs (a multiple of the SM count)
 };
 cudaError_t launch_rectify(const RectifyArgs& a, cudaStream_t s, long* launches);
 

@@ -55,9 +55,10 @@ cudaError_t launch_init_maps(const MapParams& p, int W, int H, int* map1, uint16
 }
 
 // One CTA per output tile: min/max of the (clamped) integer source coordinates of its pixels.
-__global__ void __launch_bounds__(256) tile_info_kernel(const int* __restrict__ map1, int W, int H, TileInfo* __restrict__ tiles, int tiles_x,
-                                                        int force_direct)
+__global__ void __launch_bounds__(256) tile_info_kernel(const int* __restrict__ map1, const uint16_t* __restrict__ map2, int W, int H,
+                                                        TileInfo* __restrict__ tiles, uint32_t* __restrict__ tmap, int tiles_x, int force_direct)
 {
+    __shared__ TileInfo s_t;
     const int tile = blockIdx.x;
     const int tx0 = (tile % tiles_x) * kTileW, ty0 = (tile / tiles_x) * kTileH;
     int xmin = 1 << 20, xmax = -(1 << 20), ymin = 1 << 20, ymax = -(1 << 20);
@@ -100,12 +101,32 @@ __global__ void __launch_bounds__(256) tile_info_kernel(const int* __restrict__ 
             if (x0 >= 0 && ymin >= 0 && x0 + w <= W && ymin + h <= H) t.flags |= kTileInterior;
         }
         tiles[tile] = t;
+        s_t = t;
+    }
+    __syncthreads();
+    // derived per-pixel table: word offset of the top-left tap inside the staged footprint, and the two 5-bit weights
+    const TileInfo t = s_t;
+    for (int k = threadIdx.x; k < kTileW * kTileH; k += blockDim.x) {
+        int x = tx0 + (k % kTileW), y = ty0 + (k / kTileW);
+        if (x < W && y < H) {
+            const size_t o = (size_t)y * W + x;
+            uint32_t v = 0xffffffffu;
+            if (t.w > 0) {
+                int m = map1[o];
+                int sx = max(-2, min(W, (int)(short)(m & 0xffff))), sy = max(-2, min(H, m >> 16));
+                const uint32_t off = (uint32_t)((sy - t.y0) * t.w + (sx - t.x0));
+                const uint32_t f = map2[o];
+                v = off | ((f & 31u) << 12) | (((f >> 5) & 31u) << 17);
+            }
+            tmap[o] = v;
+        }
     }
 }
 
-cudaError_t launch_tile_info(const int* map1, int W, int H, TileInfo* tiles, int tiles_x, int tiles_y, int force_direct, cudaStream_t s)
+cudaError_t launch_tile_info(const int* map1, const uint16_t* map2, int W, int H, TileInfo* tiles, uint32_t* tmap, int tiles_x, int tiles_y, int force_direct,
+                             cudaStream_t s)
 {
-    tile_info_kernel<<<tiles_x * tiles_y, 256, 0, s>>>(map1, W, H, tiles, tiles_x, force_direct);
+    tile_info_kernel<<<tiles_x * tiles_y, 256, 0, s>>>(map1, map2, W, H, tiles, tmap, tiles_x, force_direct);
     return cudaGetLastError();
 }
 

@@ -18,6 +18,10 @@
 //      shuffle + byte-permute and leave as 96-byte coalesced row segments (edge tiles: through shared memory).
 #include "common.h"
 
+#ifndef SA_BLEND_DP4A
+#define SA_BLEND_DP4A 1
+#endif
+
 namespace sa {
 
 namespace {
@@ -61,6 +65,17 @@ struct TensorT<SA_F16> { using type = __half; };
 __device__ __forceinline__ void blend(uint32_t p00, uint32_t p01, uint32_t p10, uint32_t p11, uint32_t fx, uint32_t fy, uint32_t& vB, uint32_t& vG,
                                       uint32_t& vR)
 {
+#if SA_BLEND_DP4A
+    // horizontal pass on the byte dot-product unit: (B_l, B_r, G_l, G_r) . (ax, fx, 0, 0) etc.
+    const uint32_t wx = (32u - fx) | (fx << 8), wxh = wx << 16, ay = 32u - fy;
+    const uint32_t tBG = __byte_perm(p00, p01, 0x5140), tRR = __byte_perm(p00, p01, 0x6262);
+    const uint32_t bBG = __byte_perm(p10, p11, 0x5140), bRR = __byte_perm(p10, p11, 0x6262);
+    const uint32_t tB = __dp4a(tBG, wx, 0u), tG = __dp4a(tBG, wxh, 0u), tR = __dp4a(tRR, wx, 0u);
+    const uint32_t bB = __dp4a(bBG, wx, 0u), bG = __dp4a(bBG, wxh, 0u), bR = __dp4a(bRR, wx, 0u);
+    vB = (tB * ay + bB * fy + 512u) >> 10;
+    vG = (tG * ay + bG * fy + 512u) >> 10;
+    vR = (tR * ay + bR * fy + 512u) >> 10;
+#else
     const uint32_t ax = 32u - fx, ay = 32u - fy;
     const uint32_t tBR = (p00 & 0x00ff00ffu) * ax + (p01 & 0x00ff00ffu) * fx;
     const uint32_t bBR = (p10 & 0x00ff00ffu) * ax + (p11 & 0x00ff00ffu) * fx;
@@ -69,6 +84,7 @@ __device__ __forceinline__ void blend(uint32_t p00, uint32_t p01, uint32_t p10, 
     vB = ((tBR & 0xffffu) * ay + (bBR & 0xffffu) * fy + 512u) >> 10;
     vR = ((tBR >> 16) * ay + (bBR >> 16) * fy + 512u) >> 10;
     vG = (tG * ay + bG * fy + 512u) >> 10;
+#endif
 }
 
 template <int DTYPE, bool IDENT, typename T>
@@ -118,30 +134,25 @@ __device__ __forceinline__ void tile_fast(const RectifyArgs& a, const TileInfo t
                                           const typename TensorT<DTYPE>::type* s_lut)
 {
     using T = typename TensorT<DTYPE>::type;
-    const int tid = threadIdx.x, lane = tid & 31;
-    const int W = a.W, H = a.H;
-    const int lx = tid & (kTileW - 1), ly0 = tid >> 6;
-    const int pix0 = (ty0 + ly0) * W + tx0 + lx;
+    const int tid = threadIdx.x;
+    const int W = a.W;
+    const int pix0 = (ty0 + (tid >> 6)) * W + tx0 + (tid & (kTileW - 1));
     const int rstep = 4 * W;
 
-    const int* __restrict__ map1 = eye ? a.map1[1] : a.map1[0];
-    const uint16_t* __restrict__ map2 = eye ? a.map2[1] : a.map2[0];
-    int m1[4];
-    uint32_t m2[4];
+    // per-pixel staged-footprint offset + sub-pixel weights, precomputed with the tile table (maps.cu)
+    const uint32_t* __restrict__ tmap = a.tmap[eye] + pix0;
+    uint32_t tm[4];
 #pragma unroll
-    for (int k = 0; k < 4; k++) {
-        m1[k] = __ldg(map1 + pix0 + k * rstep);
-        m2[k] = __ldg(map2 + pix0 + k * rstep);
-    }
+    for (int k = 0; k < 4; k++) tm[k] = __ldg(tmap + k * rstep);
 
-    const uint8_t* __restrict__ src = (eye ? a.src[1] : a.src[0]) + (size_t)frame * a.src_frame;
-    const int fw = ti.w, X0 = ti.x0, Y0 = ti.y0;
+    const uint8_t* __restrict__ src = a.src[eye] + (size_t)frame * a.src_frame;
+    const int fw = ti.w;
     {
         const int gw = fw >> 2, total = gw * ti.h;
         const uint32_t inv = ti.inv_gw;                        // ceil(2^20 / gw): g / gw == (g * inv) >> 20 for g < 768
         if (ALIGNED4 && (ti.flags & kTileInterior)) {
             const int pitch = (int)a.src_pitch;
-            const uint8_t* base = src + Y0 * pitch + 3 * X0;   // frame < 2 GB (checked on the host)
+            const uint8_t* base = src + ti.y0 * pitch + 3 * ti.x0;   // frame < 2 GB (checked on the host)
             for (int g = tid; g < total; g += kRectThreads) {
                 const int r = (int)(((uint32_t)g * inv) >> 20), c = g - r * gw;
                 const uint32_t* p = reinterpret_cast<const uint32_t*>(base + r * pitch + 12 * c);
@@ -154,37 +165,34 @@ __device__ __forceinline__ void tile_fast(const RectifyArgs& a, const TileInfo t
                 *reinterpret_cast<uint4*>(&s_src[g << 2]) = o;   // row stride == fw words, so word index = 4*g
             }
         } else {
+            const int X0 = ti.x0, Y0 = ti.y0;
             for (int g = tid; g < total; g += kRectThreads) {
                 const int r = (int)(((uint32_t)g * inv) >> 20), c4 = (g - r * gw) << 2;
-                *reinterpret_cast<uint4*>(&s_src[g << 2]) = stage_checked<ALIGNED4>(src, a.src_pitch, W, H, X0 + c4, Y0 + r);
+                *reinterpret_cast<uint4*>(&s_src[g << 2]) = stage_checked<ALIGNED4>(src, a.src_pitch, W, a.H, X0 + c4, Y0 + r);
             }
         }
     }
     __syncthreads();
 
-    const int plane = W * H;
-    T* __restrict__ tb = WRITE_TENSOR ? static_cast<T*>(eye ? a.tensor[1] : a.tensor[0]) + (size_t)frame * a.tensor_frame : nullptr;
-    uint32_t* __restrict__ rect32 = reinterpret_cast<uint32_t*>((eye ? a.rect[1] : a.rect[0]) + (size_t)frame * plane * 3);
-    const int m = lane & 3;
+    const int plane = W * a.H;
+    const int m = tid & 3;
     const uint32_t sel = m == 0 ? 0x4210u : (m == 1 ? 0x5421u : 0x6542u);
-    const int wbase = 3 * ((pix0 - m) >> 2) + m, wstep = 3 * W;
-    const int soff = -Y0 * fw - X0;
+    uint32_t* __restrict__ rp = reinterpret_cast<uint32_t*>(a.rect[eye] + (size_t)frame * plane * 3) + (3 * ((pix0 - m) >> 2) + m);
+    T* __restrict__ tp = WRITE_TENSOR ? static_cast<T*>(a.tensor[eye]) + (size_t)frame * a.tensor_frame + pix0 : nullptr;
+    const int wstep = 3 * W;
 #pragma unroll
     for (int k = 0; k < 4; k++) {
-        int sx = (int)(short)(m1[k] & 0xffff), sy = m1[k] >> 16;
-        sx = max(-2, min(W, sx));
-        sy = max(-2, min(H, sy));
-        const uint32_t* p = s_src + (sy * fw + sx + soff);
+        const uint32_t t = tm[k];
+        const uint32_t* p = s_src + (t & 0xfffu);
         uint32_t vB, vG, vR;
-        blend(p[0], p[1], p[fw], p[fw + 1], m2[k] & 31u, (m2[k] >> 5) & 31u, vB, vG, vR);
+        blend(p[0], p[1], p[fw], p[fw + 1], (t >> 12) & 31u, (t >> 17) & 31u, vB, vG, vR);
         const uint32_t v = vB | (vG << 8) | (vR << 16);
         const uint32_t nb = __shfl_down_sync(0xffffffffu, v, 1);
-        if (m < 3) rect32[wbase + k * wstep] = __byte_perm(v, nb, sel);
+        if (m < 3) rp[k * wstep] = __byte_perm(v, nb, sel);
         if (WRITE_TENSOR) {
             T r, g, b;
             normalise<DTYPE, IDENT, T>(s_lut, vB, vG, vR, r, g, b);
-            const int o = pix0 + k * rstep;
-            tb[o] = r; tb[o + plane] = g; tb[o + 2 * plane] = b;
+            tp[k * rstep] = r; tp[k * rstep + plane] = g; tp[k * rstep + 2 * plane] = b;
         }
     }
 }
@@ -289,6 +297,142 @@ __global__ void __launch_bounds__(kRectThreads, 6) rectify_kernel(const RectifyA
     else tile_generic<DTYPE, IDENT, WRITE_TENSOR, ALIGNED4>(a, ti, eye, frame, tx0, ty0, out_align, s_src, s_out, s_lut);
 }
 
+// ---- persistent, software-pipelined variant of the fast path ------------------------------------------------------------
+// One CTA per SM slot walks a contiguous run of tiles (in frame-fastest order consecutive tiles are the SAME tile
+// position in successive eye-frames, so the tile table entry and the per-pixel table stay L1-resident).  While tile i is
+// blended out of shared memory, the raw source words and table entries of tile i+1 are already in flight into
+// registers; they are expanded to BGRx and stored to shared memory after the barrier that ends tile i.  Global-load
+// latency therefore overlaps the arithmetic of the previous tile instead of stalling every CTA at its start.
+// Tiles that cannot take the fast path (partial tiles at the image edge, unstaged footprints) run tile_generic in place.
+template <int DTYPE, bool IDENT, bool WRITE_TENSOR>
+__global__ void __launch_bounds__(kRectThreads, 4) rectify_persistent_kernel(const RectifyArgs a, int tiles_x, int tiles_y, int out_align)
+{
+    using T = typename TensorT<DTYPE>::type;
+    __shared__ __align__(16) uint32_t s_src[kFootprintWords];
+    __shared__ __align__(16) uint32_t s_out[kTileH * kTileW * 3 / 4];
+    __shared__ T s_lut[IDENT ? 1 : 768];
+
+    const int tid = threadIdx.x;
+    const int W = a.W, H = a.H, nfe = 2 * a.n;
+    const int tpf = tiles_x * tiles_y;
+    const long long total = (long long)tpf * nfe;
+    int it = (int)(total * blockIdx.x / gridDim.x);
+    const int end = (int)(total * (blockIdx.x + 1) / gridDim.x);
+    if (it >= end) return;
+    if (!IDENT) {
+        const T* lut = static_cast<const T*>(a.lut);
+        for (int i = tid; i < 768; i += kRectThreads) s_lut[i] = lut[i];
+    }
+
+    // position of tile `it`
+    int fe, txi, tyi;
+    if (a.frame_fastest) { fe = it % nfe; const int tile = it / nfe; tyi = tile / tiles_x; txi = tile - tyi * tiles_x; }
+    else { const int tile = it % tpf; fe = it / tpf; tyi = tile / tiles_x; txi = tile - tyi * tiles_x; }
+    auto advance = [&](int& f, int& x, int& y) {
+        if (a.frame_fastest) { if (++f == nfe) { f = 0; if (++x == tiles_x) { x = 0; ++y; } } }
+        else { if (++x == tiles_x) { x = 0; if (++y == tiles_y) { y = 0; ++f; } } }
+    };
+    auto tile_fast_ok = [&](const TileInfo& t, int x, int y) { return t.w > 0 && x * kTileW + kTileW <= W && y * kTileH + kTileH <= H; };
+
+    const int pitch = (int)a.src_pitch;
+    const int rstep = 4 * W, wstep = 3 * W, plane = W * H;
+    const int m = tid & 3;
+    const uint32_t sel = m == 0 ? 0x4210u : (m == 1 ? 0x5421u : 0x6542u);
+    const int lpix = (tid >> 6) * W + (tid & (kTileW - 1));     // pixel offset of this thread inside a tile
+
+    // ---- pipeline registers: tile i+1 (table entries + raw source words), tile info of i+1 and i+2 -------------------
+    uint32_t tm_n[4], u[3][3];
+    TileInfo ti_c, ti_n;
+    int fe_n = fe, tx_n = txi, ty_n = tyi;
+
+    auto issue_loads = [&](const TileInfo& t, int f, int x, int y) {   // all loads of one fast tile, nothing consumed here
+        const int eye = f & 1, frame = f >> 1;
+        const uint32_t* __restrict__ tmap = a.tmap[eye] + (y * kTileH * W + x * kTileW + lpix);
+#pragma unroll
+        for (int k = 0; k < 4; k++) tm_n[k] = __ldg(tmap + k * rstep);
+        const uint8_t* __restrict__ src = a.src[eye] + (size_t)frame * a.src_frame;
+        const int gw = t.w >> 2, ngroups = gw * t.h;
+#pragma unroll
+        for (int j = 0; j < 3; j++) {
+            const int g = tid + j * kRectThreads;
+            u[j][0] = u[j][1] = u[j][2] = 0u;
+            if (g < ngroups) {
+                const int r = (int)(((uint32_t)g * t.inv_gw) >> 20), c = g - r * gw;
+                const int yy = t.y0 + r, xx = t.x0 + 4 * c;           // x0 and W are multiples of 4: a group is all in or all out
+                if ((unsigned)yy < (unsigned)H && (unsigned)xx < (unsigned)W) {
+                    const uint32_t* p = reinterpret_cast<const uint32_t*>(src + yy * pitch + 3 * xx);
+                    u[j][0] = __ldg(p); u[j][1] = __ldg(p + 1); u[j][2] = __ldg(p + 2);
+                }
+            }
+        }
+    };
+
+    ti_c = a.tiles[fe & 1][tyi * tiles_x + txi];
+    bool fast_c = tile_fast_ok(ti_c, txi, tyi);
+    if (fast_c) issue_loads(ti_c, fe, txi, tyi);
+    advance(fe_n, tx_n, ty_n);
+    if (it + 1 < end) ti_n = a.tiles[fe_n & 1][ty_n * tiles_x + tx_n];
+
+    for (; it < end; ++it) {
+        const int eye = fe & 1, frame = fe >> 1;
+        const int tx0 = txi * kTileW, ty0 = tyi * kTileH;
+        const bool has_next = it + 1 < end;
+        const bool fast_n = has_next && tile_fast_ok(ti_n, tx_n, ty_n);
+        if (fast_c) {
+            // expand the prefetched raw words of THIS tile into the staged footprint
+            const int ngroups = (ti_c.w >> 2) * ti_c.h;
+#pragma unroll
+            for (int j = 0; j < 3; j++) {
+                const int g = tid + j * kRectThreads;
+                if (g < ngroups) {
+                    uint4 o;
+                    o.x = u[j][0];
+                    o.y = __byte_perm(u[j][0], u[j][1], 0x4543);
+                    o.z = __byte_perm(u[j][1], u[j][2], 0x4432);
+                    o.w = u[j][2] >> 8;
+                    *reinterpret_cast<uint4*>(&s_src[g << 2]) = o;
+                }
+            }
+            uint32_t tm[4];
+#pragma unroll
+            for (int k = 0; k < 4; k++) tm[k] = tm_n[k];
+            __syncthreads();
+            if (fast_n) issue_loads(ti_n, fe_n, tx_n, ty_n);            // tile i+1 in flight during the blend of tile i
+
+            const int fw = ti_c.w;
+            const int pix0 = ty0 * W + tx0 + lpix;
+            uint32_t* __restrict__ rp = reinterpret_cast<uint32_t*>(a.rect[eye] + (size_t)frame * plane * 3) + (3 * ((pix0 - m) >> 2) + m);
+            T* __restrict__ tp = WRITE_TENSOR ? static_cast<T*>(a.tensor[eye]) + (size_t)frame * a.tensor_frame + pix0 : nullptr;
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const uint32_t t = tm[k];
+                const uint32_t* p = s_src + (t & 0xfffu);
+                uint32_t vB, vG, vR;
+                blend(p[0], p[1], p[fw], p[fw + 1], (t >> 12) & 31u, (t >> 17) & 31u, vB, vG, vR);
+                const uint32_t v = vB | (vG << 8) | (vR << 16);
+                const uint32_t nb = __shfl_down_sync(0xffffffffu, v, 1);
+                if (m < 3) rp[k * wstep] = __byte_perm(v, nb, sel);
+                if (WRITE_TENSOR) {
+                    T r, g, b;
+                    normalise<DTYPE, IDENT, T>(s_lut, vB, vG, vR, r, g, b);
+                    tp[k * rstep] = r; tp[k * rstep + plane] = g; tp[k * rstep + 2 * plane] = b;
+                }
+            }
+            __syncthreads();                                            // everyone is done reading s_src
+        } else {
+            __syncthreads();                                            // (also orders the LUT fill before its first use)
+            tile_generic<DTYPE, IDENT, WRITE_TENSOR, true>(a, ti_c, eye, frame, tx0, ty0, out_align, s_src, s_out, s_lut);
+            __syncthreads();
+            if (fast_n) issue_loads(ti_n, fe_n, tx_n, ty_n);
+        }
+        // rotate the pipeline
+        fe = fe_n; txi = tx_n; tyi = ty_n;
+        ti_c = ti_n; fast_c = fast_n;
+        advance(fe_n, tx_n, ty_n);
+        if (it + 2 < end) ti_n = a.tiles[fe_n & 1][ty_n * tiles_x + tx_n];
+    }
+}
+
 // rectify = 0 (images already rectified) and the tail of the resize path: BGR u8 -> normalised planes only.
 template <int DTYPE, bool IDENT>
 __global__ void __launch_bounds__(256) preprocess_kernel(const PreprocArgs a)
@@ -323,6 +467,13 @@ inline bool lut_is_identity(int model) { return model == SA_MODEL_RAFTSTEREO || 
 template <int DTYPE, bool IDENT, bool WT>
 cudaError_t launch_rectify_t(const RectifyArgs& a, bool aligned4, int tiles_x, int out_align, int fast_ok, dim3 grid, cudaStream_t s)
 {
+    if (fast_ok && aligned4 && a.persistent_ctas > 0) {
+        const int tiles_y = (a.H + kTileH - 1) / kTileH;
+        const long long total = (long long)tiles_x * tiles_y * 2 * a.n;
+        const unsigned ctas = (unsigned)(total < a.persistent_ctas ? total : a.persistent_ctas);
+        rectify_persistent_kernel<DTYPE, IDENT, WT><<<ctas, kRectThreads, 0, s>>>(a, tiles_x, tiles_y, out_align);
+        return cudaGetLastError();
+    }
     if (aligned4) rectify_kernel<DTYPE, IDENT, WT, true><<<grid, kRectThreads, 0, s>>>(a, tiles_x, out_align, fast_ok);
     else rectify_kernel<DTYPE, IDENT, WT, false><<<grid, kRectThreads, 0, s>>>(a, tiles_x, out_align, fast_ok);
     return cudaGetLastError();

@@ -81,15 +81,17 @@ def test_maps_absurd_calibrations(golden, calibs, tag):
 
 # ---- a3: rectified images -------------------------------------------------------------------------------------
 @pytest.mark.parametrize("name", ["calib_a", "calib_b", "calib_c_rational"])
-@pytest.mark.parametrize("variant", ["default", "tile_fastest", "force_direct", "force_generic"])
+@pytest.mark.parametrize("variant", ["default", "tile_fastest", "force_direct", "force_generic", "persistent", "persistent_tile_fastest"])
 def test_rectified_demo_bit_exact(golden, demo_pair, name, variant):
     g_ = golden["cases"]["demo_" + name]
     l, r = demo_pair
     with geom(640, 480, model="RAFTStereo") as g:
         if variant == "force_direct":
             g.set_option("force_direct", 1)
-        if variant == "tile_fastest":
+        if variant.endswith("tile_fastest"):
             g.set_option("frame_fastest", 0)
+        if variant.startswith("persistent"):
+            g.set_option("persistent", 4)
         if variant == "force_generic":
             g.set_option("force_generic", 1)
         g.load_calibration_yaml(os.path.join(GOLDEN, name + ".yml"))
@@ -103,11 +105,13 @@ def test_rectified_scaled_bit_exact(golden, calibs, name):
     g_ = golden["cases"]["scaled_" + name]
     c, (W, H) = scaled_case(calibs, name)
     li, ri = O.synthetic_image(W, H, g_["image_seeds"][0]), O.synthetic_image(W, H, g_["image_seeds"][1])
-    with geom(W, H, model="CREStereo") as g:
-        g.set_calibration(c)
-        g.rectify_preprocess(li[None], ri[None])
-        assert md5(g.rectified(1, 0)[0]) == g_["rect_left"], name
-        assert md5(g.rectified(1, 1)[0]) == g_["rect_right"], name
+    for persistent in (4, 0):
+        with geom(W, H, model="CREStereo") as g:
+            g.set_option("persistent", persistent)
+            g.set_calibration(c)
+            g.rectify_preprocess(li[None], ri[None])
+            assert md5(g.rectified(1, 0)[0]) == g_["rect_left"], name
+            assert md5(g.rectified(1, 1)[0]) == g_["rect_right"], name
 
 
 def test_rectified_batch_device_input_and_pitch(calibs, demo_pair):
