@@ -293,16 +293,10 @@ def main():
     rep_ms, rep_cnt = g.stage_time(SL.STAGE_REPROJECT)
     heat_ms, _ = g.stage_time(SL.STAGE_HEATMAP) if args.heatmap else (0.0, 0)
     dev_ms = rect_ms + rep_ms + heat_ms                      # sum of the per-kernel event pairs
-    tt = torch.tensor([step_time, dev_ms / 1e3, float(launches)], dtype=torch.float64, device="cuda")
-    if world > 1:
-        mx = tt.clone()
-        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
-        sm = tt.clone()
-        dist.all_reduce(sm, op=dist.ReduceOp.SUM)
-        step_time, dev_s, launches = float(mx[0]), float(mx[1]), int(sm[2])
-    else:
-        dev_s = dev_ms / 1e3
-    value = world * n * args.steps / step_time
+    from stereoalgorithms_b200 import sharding
+    pairs_total, step_time, launches = sharding.aggregate(n * args.steps, step_time, launches)     # SUM pairs, MAX time, SUM launches
+    _, dev_s, _ = sharding.aggregate(0, dev_ms / 1e3)
+    value = pairs_total / step_time
 
     # ---- e2e: host buffers through the reference-facing call --------------------------------------------------------
     e2e = None
@@ -325,14 +319,12 @@ def main():
         for _ in range(k2):
             e2e_step()                                        # synchronous: returns when the results are in host memory
         el2 = time.perf_counter() - t0
-        t2 = torch.tensor([el2], dtype=torch.float64, device="cuda")
-        if world > 1:
-            dist.all_reduce(t2, op=dist.ReduceOp.MAX)
+        pairs2, t2, _ = sharding.aggregate(n * k2, el2)
         h2d = 2 * n * npix * 3
         d2h = n * npix * (24 + 4 + 6)
-        e2e = {"value": world * n * k2 / float(t2[0]), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": k2,
+        e2e = {"value": pairs2 / t2, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": k2,
                "api": "sa_run_batch (pinned host images in; point cloud + disparity + rectified L/R out)",
-               "pcie_gbs": (h2d + d2h) * k2 / float(t2[0]) / 1e9}
+               "pcie_gbs_per_gpu": (h2d + d2h) * k2 / t2 / 1e9}
     t_wall2 = time.time()
     clocks = sampler.stop(t_wall0, t_wall2) if sampler else None
 

@@ -108,3 +108,30 @@ def test_other_image_size_than_640x480(calibs):
     want, _ = O.reproject_dense(O.FASTACVNET_PLUS, d.array, img, calibs["calib_b"]["Q"])
     _check_points(pc.reshape(-1, 6), want)
     F.Release(p)
+
+
+def test_cpp_shim_demo_program(demo_pair, calibs, tmp_path):
+    """shims/FastACVNet_plus_Algorithm.cpp compiled against the stand-in cv::Mat, driven by a cut-down copy of the
+    reference's demo main (tests/shim_demo.cpp): the C++ route into the library, end to end."""
+    import subprocess
+    from conftest import ROOT
+    from test_shims_cpu import build_shim
+    so = build_shim("FastACVNet_plus_Algorithm", tmp_path)
+    exe = str(tmp_path / "shim_demo")
+    subprocess.check_call(["g++", "-std=c++17", "-O1", "-I", os.path.join(ROOT, "tests", "fake_opencv"), "-o", exe,
+                           os.path.join(ROOT, "tests", "shim_demo.cpp"), so, "-Wl,-rpath," + str(tmp_path)])
+    l, r = demo_pair
+    l.tofile(str(tmp_path / "l.bgr"))
+    r.tofile(str(tmp_path / "r.bgr"))
+    out = subprocess.run([exe, CALIB, str(tmp_path / "l.bgr"), str(tmp_path / "r.bgr"), "640", "480", str(tmp_path / "o")],
+                         capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr
+    assert out.stdout.strip() == "FastACVNet_plus_Algorithm_V1.0"
+    c = calibs["calib_b"]
+    rl, rr = O.rectify_pair(c, l, r)
+    assert np.array_equal(np.fromfile(str(tmp_path / "o_rect_left.bgr"), np.uint8).reshape(480, 640, 3), rl)
+    assert np.array_equal(np.fromfile(str(tmp_path / "o_rect_right.bgr"), np.uint8).reshape(480, 640, 3), rr)
+    d = np.fromfile(str(tmp_path / "o_disparity.f32"), np.float32).reshape(480, 640)
+    pts = np.fromfile(str(tmp_path / "o_pointcloud.f32"), np.float32).reshape(-1, 6)
+    want, _ = O.reproject_dense(O.FASTACVNET_PLUS, d, rl, c["Q"])
+    _check_points(pts, want)
