@@ -171,6 +171,29 @@ SA_API int sa_parse_calibration_yaml(const char* path, sa_calibration* out, char
 SA_API int sa_norm_lut(int model, float* lut768);
 SA_API int sa_resize_table(int dst, int src, int* table);
 
+/* No counterpart in the reference.  Compacting reprojection (the SA_COMPACT flavour of sa_reproject) for callers that are
+ * not allowed to allocate device memory at the point where they need it - a TensorRT plugin's enqueue(), a camera / ROS
+ * callback under a "no allocation after start-up" rule, a process whose own pool already owns the whole GPU.  It takes no
+ * handle and calls no cudaMalloc / cudaFree or any other allocating routine: the per-CTA counts and offsets the
+ * compaction needs live in a 512 KiB device array built into the library (present on every GPU that loads it, until
+ * the process exits).
+ *   Limit: ceil(w*h / 1024) * n <= 65536 scratch slots per call (218 frames of 640x480, 32 of 1920x1080, 8 of
+ *   3840x2160); beyond that the call returns SA_ERR_TOO_LARGE and explains itself in `err`.
+ *   All image/point pointers are DEVICE pointers on the CURRENT device (there is no handle to select one); Q16 is 16
+ *   host floats, row-major.  Strides of 0 mean "contiguous" (left_pitch = 3*w, frame strides = one frame).
+ *   disparity [n][..] float (sign-flipped in place when negate != 0, like RAFTStereo's kernel), left_bgr the rectified
+ *   left images, points [n][w*h][6] with the first counts[i] rows of frame i valid, counts [n] ints on the device.
+ *   Work is queued on `stream` (NULL = the default stream); nothing is synchronised.
+ *   The first call on each device also looks up the scratch array's device address; make that first call before any
+ *   stream capture is started.
+ *   All calls share the one scratch array: calls that can overlap on the GPU (different streams, different threads)
+ *   race on it and corrupt each other's point counts - serialise them.  The array keeps whatever the previous call
+ *   wrote; that is harmless because every slot a call reads is written by that same call first.
+ *   err (optional, err_len bytes) receives the failure text. */
+SA_API int sa_reproject_compact_noalloc(float* disparity, size_t disparity_frame_stride, const uint8_t* left_bgr, size_t left_pitch,
+                                        size_t left_frame_stride, const float* Q16, int w, int h, int n, int negate, float* points, int* counts,
+                                        sa_stream stream, char* err, size_t err_len);
+
 /* Pinned host memory for the buffers above (cudaMallocHost of TRTFastACVNet_plus.cpp:98-99). */
 SA_API int sa_host_alloc(void** p, size_t bytes);
 SA_API int sa_host_free(void* p);

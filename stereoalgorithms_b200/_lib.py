@@ -70,6 +70,7 @@ SIGNATURES = {
     "sa_parse_calibration_yaml": (_i, [_cp, C.POINTER(sa_calibration), C.c_char_p, _sz]),
     "sa_norm_lut": (_i, [_i, _vp]),
     "sa_resize_table": (_i, [_i, _i, _vp]),
+    "sa_reproject_compact_noalloc": (_i, [_vp, _sz, _vp, _sz, _sz, _vp, _i, _i, _i, _i, _vp, _vp, _vp, C.c_char_p, _sz]),
     "sa_host_alloc": (_i, [C.POINTER(_vp), _sz]),
     "sa_host_free": (_i, [_vp]),
     "sa_stage_time": (_i, [_vp, _i, C.POINTER(C.c_double), C.POINTER(C.c_long)]),

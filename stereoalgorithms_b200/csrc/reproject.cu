@@ -15,8 +15,10 @@
 // Compact mode (extension): keep pixels with finite disparity > 0, in row-major order.
 // Three launches: per-block counts -> per-frame exclusive scan -> reproject with a warp-ballot style prefix
 // (4-bit masks, shuffle scan) so that every warp writes one contiguous run of points.
+#include <atomic>
 #include <cfloat>
 #include <cmath>
+#include <cstdarg>
 
 #include "common.h"
 
@@ -390,3 +392,98 @@ cudaError_t launch_reproject(const ReprojectArgs& a, cudaStream_t s, long* launc
 }
 
 }  // namespace sa
+
+// =============================================================================================================
+// sa_reproject_compact_noalloc: compacting reprojection for callers that may not allocate device memory.
+//
+// The compaction kernels above need scratch memory beyond their inputs and outputs: one valid-pixel count and one
+// prefix offset per CTA of 1024 pixels.  sa_reproject takes that scratch from buffers the handle cudaMalloc'ed in
+// sa_create.  Some callers can never reach a point where allocating is allowed: a TensorRT plugin's enqueue(), a
+// camera or ROS callback that runs under a "no allocation after start-up" rule, or a process whose own memory pool
+// has already claimed the whole device, so that a later cudaMalloc simply fails.  For them the scratch lives in the
+// library image itself: a file-scope device array, reserved on every GPU that loads the library, for as long as the
+// process lives.  The price is a fixed ceiling (kNoAllocMaxBlocks CTAs per call) and no concurrency between calls.
+namespace sa {
+namespace {
+
+constexpr int kNoAllocMaxBlocks = 65536;   // 1024-pixel CTAs over all frames of one call: 218 frames of 640x480, 32 of 1080p, 8 of 4K
+
+// counts in [0, kNoAllocMaxBlocks), offsets in [kNoAllocMaxBlocks, 2 * kNoAllocMaxBlocks): 512 KiB on each GPU.
+static __device__ __align__(256) int g_noalloc_scratch[2 * kNoAllocMaxBlocks];
+
+// In host code `g_noalloc_scratch` is only a handle for the runtime, not an address a kernel could use; the address is
+// looked up once per device (with that device current) and remembered here.
+constexpr int kNoAllocMaxDevices = 64;
+static std::atomic<int*> g_noalloc_addr[kNoAllocMaxDevices];
+
+int noalloc_fail(char* err, size_t err_len, int code, const char* fmt, ...)
+{
+    if (err && err_len) {
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(err, err_len, fmt, ap);
+        va_end(ap);
+    }
+    return code;
+}
+
+}  // namespace
+}  // namespace sa
+
+extern "C" int sa_reproject_compact_noalloc(float* disparity, size_t disparity_frame_stride, const uint8_t* left_bgr, size_t left_pitch,
+                                            size_t left_frame_stride, const float* Q16, int w, int h, int n, int negate, float* points, int* counts,
+                                            sa_stream stream, char* err, size_t err_len)
+{
+    using namespace sa;
+    if (err && err_len) err[0] = 0;
+    if (!disparity || !left_bgr || !Q16 || !points || !counts)
+        return noalloc_fail(err, err_len, SA_ERR_INVALID_ARG, "sa_reproject_compact_noalloc: null pointer argument");
+    if (w <= 0 || h <= 0 || w > 16384 || h > 16384 || n <= 0)
+        return noalloc_fail(err, err_len, SA_ERR_INVALID_ARG, "sa_reproject_compact_noalloc: bad size %dx%d x %d frames", w, h, n);
+    if (left_pitch == 0) left_pitch = (size_t)w * 3;
+    if (left_pitch < (size_t)w * 3) return noalloc_fail(err, err_len, SA_ERR_INVALID_ARG, "sa_reproject_compact_noalloc: left_pitch %zu < 3*w", left_pitch);
+    if (disparity_frame_stride == 0) disparity_frame_stride = (size_t)w * h;
+    if (left_frame_stride == 0) left_frame_stride = left_pitch * (size_t)h;
+    const long long nblk = reproject_blocks_per_frame(w, h);
+    if (nblk * n > kNoAllocMaxBlocks)
+        return noalloc_fail(err, err_len, SA_ERR_TOO_LARGE,
+                            "sa_reproject_compact_noalloc: %d frames of %dx%d need %lld scratch slots, the built-in scratch holds %d "
+                            "(one slot per 1024 pixels per frame); split the call or use sa_reproject",
+                            n, w, h, nblk * n, kNoAllocMaxBlocks);
+
+    // set-up, once per device: resolve the device address of the scratch array for the CURRENT device
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return noalloc_fail(err, err_len, SA_ERR_CUDA, "cudaGetDevice: %s", cudaGetErrorString(e));
+    if (dev < 0 || dev >= kNoAllocMaxDevices) return noalloc_fail(err, err_len, SA_ERR_INVALID_ARG, "device ordinal %d not supported (max %d)", dev, kNoAllocMaxDevices - 1);
+    int* scratch = g_noalloc_addr[dev].load(std::memory_order_acquire);
+    if (!scratch) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p) return noalloc_fail(err, err_len, SA_ERR_CUDA, "cudaGetSymbolAddress(scratch) on device %d: %s", dev, cudaGetErrorString(e));
+        scratch = static_cast<int*>(p);
+        g_noalloc_addr[dev].store(scratch, std::memory_order_release);   // racing first calls resolve the same address
+    }
+
+    ReprojectArgs a{};
+    a.disp = disparity;
+    a.disp_frame = disparity_frame_stride;
+    a.color = left_bgr;
+    a.color_pitch = left_pitch;
+    a.color_frame = left_frame_stride;
+    a.points = points;
+    for (int i = 0; i < 16; i++) a.q[i] = Q16[i];
+    a.w = w; a.h = h; a.n = n;
+    a.negate = negate ? 1 : 0;
+    a.compact = 1;
+    a.exact_div = 0;
+    a.blk_minmax = nullptr;
+    // Every slot this call reads is written by this call first (count kernel -> scan kernel -> compaction), so nothing
+    // has to be zeroed; whatever the previous call left behind in the rest of the array is never looked at.
+    a.blk_counts = scratch;
+    a.blk_offsets = scratch + kNoAllocMaxBlocks;
+    a.counts = counts;
+    e = launch_reproject(a, static_cast<cudaStream_t>(stream), nullptr);
+    if (e != cudaSuccess) return noalloc_fail(err, err_len, SA_ERR_CUDA, "kernel launch: %s", cudaGetErrorString(e));
+    return SA_OK;
+}
