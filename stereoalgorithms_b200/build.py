@@ -26,7 +26,8 @@ def _deps_mtime() -> float:
 
 def _compile(src: str, verbose: bool) -> str:
     obj = os.path.join(OBJ, src + ".o")
-    cmd = ["nvcc", *NVCC_FLAGS, "-x", "cu", "-c", os.path.join(CSRC, src), "-o", obj]
+    extra = os.environ.get("SA_EXTRA_NVCC_FLAGS", "").split()      # tuning experiments, e.g. -DSA_BATCH_MINB=3
+    cmd = ["nvcc", *NVCC_FLAGS, *extra, "-x", "cu", "-c", os.path.join(CSRC, src), "-o", obj]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("nvcc failed for %s:\n%s\n%s" % (src, r.stdout, r.stderr))

@@ -181,6 +181,7 @@ static int stage_rectify(sa_handle* h, int f0, int n, const uint8_t* src_l, cons
         a.frame_fastest = (int)h->opt_frame_fastest;
         a.force_generic = (int)h->opt_force_generic;
         a.persistent_ctas = (int)(h->opt_persistent > 0 ? h->opt_persistent * h->sm_count : 0);
+        a.batch_loop = h->opt_batch_loop ? h->sm_count : 0;
         {
             StageScope t(h, SA_STAGE_RECTIFY, s);
             SA_CUDA(h, launch_rectify(a, s, &h->launches));
@@ -827,6 +828,7 @@ int sa_set_option(sa_handle* h, const char* key, long value)
     else if (!std::strcmp(key, "force_generic")) h->opt_force_generic = value;
     else if (!std::strcmp(key, "exact_div")) h->opt_exact_div = value;
     else if (!std::strcmp(key, "persistent")) h->opt_persistent = value;
+    else if (!std::strcmp(key, "batch_loop")) h->opt_batch_loop = value;
     else return fail(h, SA_ERR_INVALID_ARG, "sa_set_option: unknown key '%s'", key);
     return SA_OK;
 }

@@ -100,6 +100,7 @@ struct sa_handle {
     long opt_force_generic = 0;
     long opt_exact_div = 0;
     long opt_persistent = 0;          // CTAs per SM of the persistent rectify kernel (0 = one CTA per tile, the default: measured faster)
+    long opt_batch_loop = 1;          // rectify_batch_kernel (default); 0 = one CTA per (tile, eye, frame)
     int sm_count = 148;
 
     long launches = 0;
@@ -156,6 +157,7 @@ struct RectifyArgs {
     int frame_fastest;
     int force_generic;                 // testing: never take the fast tile path
     int persistent_ctas;               // > 0: persistent pipelined kernel with this many CTAs (a multiple of the SM count)
+    int batch_loop;                    // > 0 (= SM count): one CTA per (tile, eye) walks a run of frames (rectify_batch_kernel)
 };
 cudaError_t launch_rectify(const RectifyArgs& a, cudaStream_t s, long* launches);
 

@@ -433,6 +433,152 @@ __global__ void __launch_bounds__(kRectThreads, 4) rectify_persistent_kernel(con
     }
 }
 
+// ---- batch-loop variant: the tile is fixed, the CTA walks the frames --------------------------------------------------
+// Everything that depends only on the calibration - the tile's footprint box, each thread's staging addresses and
+// bounds predicates, the per-pixel footprint offsets and blend weights, the output offsets - is the same for every frame
+// of the batch.  So a CTA takes one (tile, eye) and a run of frames: it sets those values up once, keeps them in
+// registers, and per frame only (a) stores the previously fetched raw source words into the staged footprint,
+// (b) issues the loads of the NEXT frame's words, (c) blends and stores its four pixels.  Per-frame work shrinks to the
+// arithmetic that really depends on the pixels, and the global loads of frame f+1 are in flight during the blend of f.
+// grid = (tiles_x, tiles_y, 2 * chunks), blockIdx.z = eye + 2 * chunk, chunk c covers frames [c*F, min(n, (c+1)*F)).
+#ifndef SA_BATCH_MINB
+#define SA_BATCH_MINB 4
+#endif
+#ifndef SA_BATCH_L2_PREFETCH
+#define SA_BATCH_L2_PREFETCH 1
+#endif
+template <int DTYPE, bool IDENT, bool WRITE_TENSOR>
+__global__ void __launch_bounds__(kRectThreads, SA_BATCH_MINB) rectify_batch_kernel(const RectifyArgs a, int tiles_x, int out_align, int frames_per_cta)
+{
+    using T = typename TensorT<DTYPE>::type;
+    __shared__ __align__(16) uint32_t s_src2[2][kFootprintWords];   // double buffered: one barrier per frame
+    uint32_t* const s_src = s_src2[0];
+    uint32_t* const s_out = s_src2[1];                               // only the generic path needs s_out; it never overlaps the loop below
+    __shared__ T s_lut[IDENT ? 1 : 768];
+
+    const int tid = threadIdx.x;
+    const int W = a.W, H = a.H;
+    const int eye = blockIdx.z & 1, chunk = blockIdx.z >> 1;
+    const int f0 = chunk * frames_per_cta, f1 = min(a.n, f0 + frames_per_cta);
+    const int tx0 = blockIdx.x * kTileW, ty0 = blockIdx.y * kTileH;
+    const TileInfo ti = a.tiles[eye][blockIdx.y * tiles_x + blockIdx.x];
+    if (!IDENT) {
+        const T* lut = static_cast<const T*>(a.lut);
+        for (int i = tid; i < 768; i += kRectThreads) s_lut[i] = lut[i];
+    }
+    if (!(ti.w > 0 && tx0 + kTileW <= W && ty0 + kTileH <= H)) {      // edge tile / unstaged footprint: generic path, frame by frame
+        for (int f = f0; f < f1; f++) {
+            __syncthreads();
+            tile_generic<DTYPE, IDENT, WRITE_TENSOR, true>(a, ti, eye, f, tx0, ty0, out_align, s_src, s_out, s_lut);
+        }
+        return;
+    }
+
+    // ---- per-calibration state of this thread (frame independent) ----------------------------------------------
+    const int pix0 = (ty0 + (tid >> 6)) * W + tx0 + (tid & (kTileW - 1));
+    const int rstep = 4 * W, wstep = 3 * W, plane = W * H;
+    uint32_t toff[4], twt[4];           // byte offset of the top-left tap in s_src; (32-fx, fx, 32-fy, fy) as four bytes
+    {
+        const uint32_t* __restrict__ tmap = a.tmap[eye] + pix0;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const uint32_t t = __ldg(tmap + k * rstep);
+            const uint32_t fx = (t >> 12) & 31u, fy = (t >> 17) & 31u;
+            toff[k] = (t & 0xfffu) << 2;
+            twt[k] = (32u - fx) | (fx << 8) | ((32u - fy) << 16) | (fy << 24);
+        }
+    }
+    const int fw4 = ti.w << 2;          // bytes per staged row
+    const int ngroups = (ti.w >> 2) * ti.h;
+    const int pitch = (int)a.src_pitch;
+    int soff[3];                        // byte offset of this thread's staging groups inside a frame; -1 = nothing to load
+#pragma unroll
+    for (int j = 0; j < 3; j++) {
+        const int g = tid + j * kRectThreads;
+        soff[j] = -1;
+        if (g < ngroups) {
+            const int gw = ti.w >> 2;
+            const int r = (int)(((uint32_t)g * ti.inv_gw) >> 20), c = g - r * gw;
+            const int yy = ti.y0 + r, xx = ti.x0 + 4 * c;             // x0 and W are multiples of 4: a group is all in or all out
+            if ((unsigned)yy < (unsigned)H && (unsigned)xx < (unsigned)W) soff[j] = yy * pitch + 3 * xx;
+        }
+    }
+    const int m = tid & 3;
+    uint32_t sel = m == 0 ? 0x4210u : (m == 1 ? 0x5421u : 0x6542u);
+    asm volatile("" : "+r"(sel));       // keep it in a register: recomputing the selects inside the frame loop costs 5 instructions per pixel
+    const uint8_t* __restrict__ src = a.src[eye] + (size_t)f0 * a.src_frame;
+    uint32_t* __restrict__ rp = reinterpret_cast<uint32_t*>(a.rect[eye] + (size_t)f0 * plane * 3) + (3 * ((pix0 - m) >> 2) + m);
+    T* __restrict__ tp = WRITE_TENSOR ? static_cast<T*>(a.tensor[eye]) + (size_t)f0 * a.tensor_frame + pix0 : nullptr;
+    const size_t rect_frame_words = (size_t)plane * 3 / 4;
+
+    uint32_t u[3][3];
+    auto fetch = [&](const uint8_t* __restrict__ base) {
+#pragma unroll
+        for (int j = 0; j < 3; j++) {
+            u[j][0] = u[j][1] = u[j][2] = 0u;
+            if (j * kRectThreads < ngroups && soff[j] >= 0) {
+                const uint32_t* p = reinterpret_cast<const uint32_t*>(base + soff[j]);
+                u[j][0] = __ldg(p); u[j][1] = __ldg(p + 1); u[j][2] = __ldg(p + 2);
+            }
+        }
+    };
+    fetch(src);
+
+    for (int f = f0; f < f1; f++) {
+        uint32_t* const buf = s_src2[(f - f0) & 1];
+#pragma unroll
+        for (int j = 0; j < 3; j++) {
+            const int g = tid + j * kRectThreads;
+            if (g < ngroups) {
+                uint4 o;
+                o.x = u[j][0];
+                o.y = __byte_perm(u[j][0], u[j][1], 0x4543);
+                o.z = __byte_perm(u[j][1], u[j][2], 0x4432);
+                o.w = u[j][2] >> 8;
+                *reinterpret_cast<uint4*>(&buf[g << 2]) = o;
+            }
+        }
+        __syncthreads();      // the only barrier of the iteration: the other buffer was last read before the previous one
+        if (f + 1 < f1) { src += a.src_frame; fetch(src); }            // next frame's words fly during this frame's blend
+#if SA_BATCH_L2_PREFETCH
+        if (f + 2 < f1) {                                               // and the frame after that is pulled into L2, so that
+            const uint8_t* nxt = src + a.src_frame;                     // next iteration's fetch is an L2 hit, not a DRAM round trip
+#pragma unroll
+            for (int j = 0; j < 3; j++)
+                if (j * kRectThreads < ngroups && soff[j] >= 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(nxt + soff[j]));
+        }
+#endif
+
+        const char* sb = reinterpret_cast<const char*>(buf);
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const char* p = sb + toff[k];
+            const uint32_t p00 = *reinterpret_cast<const uint32_t*>(p), p01 = *reinterpret_cast<const uint32_t*>(p + 4);
+            const uint32_t p10 = *reinterpret_cast<const uint32_t*>(p + fw4), p11 = *reinterpret_cast<const uint32_t*>(p + fw4 + 4);
+            const uint32_t wt = twt[k];
+            const uint32_t wx = wt & 0xffffu, wxh = wt << 16;
+            const uint32_t tBG = __byte_perm(p00, p01, 0x5140), tRR = __byte_perm(p00, p01, 0x6262);
+            const uint32_t bBG = __byte_perm(p10, p11, 0x5140), bRR = __byte_perm(p10, p11, 0x6262);
+            const uint32_t tB = __dp4a(tBG, wx, 0u), tG = __dp4a(tBG, wxh, 0u), tR = __dp4a(tRR, wx, 0u);
+            const uint32_t bB = __dp4a(bBG, wx, 0u), bG = __dp4a(bBG, wxh, 0u), bR = __dp4a(bRR, wx, 0u);
+            // vertical pass: (t, b) as two 16-bit lanes . (32-fy, fy) = bytes 2,3 of wt, plus the rounding constant
+            const uint32_t vB = __dp2a_hi(__byte_perm(tB, bB, 0x5410), wt, 512u) >> 10;
+            const uint32_t vG = __dp2a_hi(__byte_perm(tG, bG, 0x5410), wt, 512u) >> 10;
+            const uint32_t vR = __dp2a_hi(__byte_perm(tR, bR, 0x5410), wt, 512u) >> 10;
+            const uint32_t v = vB | (vG << 8) | (vR << 16);
+            const uint32_t nb = __shfl_down_sync(0xffffffffu, v, 1);
+            if (m < 3) rp[k * wstep] = __byte_perm(v, nb, sel);
+            if (WRITE_TENSOR) {
+                T r, g, b;
+                normalise<DTYPE, IDENT, T>(s_lut, vB, vG, vR, r, g, b);
+                tp[k * rstep] = r; tp[k * rstep + plane] = g; tp[k * rstep + 2 * plane] = b;
+            }
+        }
+        rp += rect_frame_words;
+        if (WRITE_TENSOR) tp += a.tensor_frame;
+    }
+}
+
 // rectify = 0 (images already rectified) and the tail of the resize path: BGR u8 -> normalised planes only.
 template <int DTYPE, bool IDENT>
 __global__ void __launch_bounds__(256) preprocess_kernel(const PreprocArgs a)
@@ -467,6 +613,20 @@ inline bool lut_is_identity(int model) { return model == SA_MODEL_RAFTSTEREO || 
 template <int DTYPE, bool IDENT, bool WT>
 cudaError_t launch_rectify_t(const RectifyArgs& a, bool aligned4, int tiles_x, int out_align, int fast_ok, dim3 grid, cudaStream_t s)
 {
+    if (fast_ok && aligned4 && a.batch_loop) {
+        const int tiles_y = (a.H + kTileH - 1) / kTileH;
+        // frames per CTA: enough CTAs for ~8 per SM slot (balance), as many frames per CTA as that allows (amortisation)
+        const long long tile_eyes = (long long)tiles_x * tiles_y * 2;
+        long long want = a.batch_loop * 8LL;                         // a.batch_loop carries the SM count
+        int fpc = (int)((tile_eyes * a.n + want - 1) / want);
+        if (fpc < 1) fpc = 1;
+        if (fpc > a.n) fpc = a.n;
+        const int chunks = (a.n + fpc - 1) / fpc;
+        if (2 * chunks <= 65535) {
+            rectify_batch_kernel<DTYPE, IDENT, WT><<<dim3((unsigned)tiles_x, (unsigned)tiles_y, 2u * (unsigned)chunks), kRectThreads, 0, s>>>(a, tiles_x, out_align, fpc);
+            return cudaGetLastError();
+        }
+    }
     if (fast_ok && aligned4 && a.persistent_ctas > 0) {
         const int tiles_y = (a.H + kTileH - 1) / kTileH;
         const long long total = (long long)tiles_x * tiles_y * 2 * a.n;

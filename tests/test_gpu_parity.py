@@ -81,7 +81,7 @@ def test_maps_absurd_calibrations(golden, calibs, tag):
 
 # ---- a3: rectified images -------------------------------------------------------------------------------------
 @pytest.mark.parametrize("name", ["calib_a", "calib_b", "calib_c_rational"])
-@pytest.mark.parametrize("variant", ["default", "tile_fastest", "force_direct", "force_generic", "persistent", "persistent_tile_fastest"])
+@pytest.mark.parametrize("variant", ["default", "tile_fastest", "force_direct", "force_generic", "persistent", "persistent_tile_fastest", "per_tile_cta"])
 def test_rectified_demo_bit_exact(golden, demo_pair, name, variant):
     g_ = golden["cases"]["demo_" + name]
     l, r = demo_pair
@@ -91,7 +91,10 @@ def test_rectified_demo_bit_exact(golden, demo_pair, name, variant):
         if variant.endswith("tile_fastest"):
             g.set_option("frame_fastest", 0)
         if variant.startswith("persistent"):
+            g.set_option("batch_loop", 0)
             g.set_option("persistent", 4)
+        if variant in ("per_tile_cta", "tile_fastest", "force_generic"):
+            g.set_option("batch_loop", 0)
         if variant == "force_generic":
             g.set_option("force_generic", 1)
         g.load_calibration_yaml(os.path.join(GOLDEN, name + ".yml"))
@@ -105,8 +108,9 @@ def test_rectified_scaled_bit_exact(golden, calibs, name):
     g_ = golden["cases"]["scaled_" + name]
     c, (W, H) = scaled_case(calibs, name)
     li, ri = O.synthetic_image(W, H, g_["image_seeds"][0]), O.synthetic_image(W, H, g_["image_seeds"][1])
-    for persistent in (4, 0):
+    for batch_loop, persistent in ((1, 0), (0, 4), (0, 0)):
         with geom(W, H, model="CREStereo") as g:
+            g.set_option("batch_loop", batch_loop)
             g.set_option("persistent", persistent)
             g.set_calibration(c)
             g.rectify_preprocess(li[None], ri[None])
