@@ -511,41 +511,49 @@ __global__ void __launch_bounds__(kRectThreads, SA_BATCH_MINB) rectify_batch_ker
     T* __restrict__ tp = WRITE_TENSOR ? static_cast<T*>(a.tensor[eye]) + (size_t)f0 * a.tensor_frame + pix0 : nullptr;
     const size_t rect_frame_words = (size_t)plane * 3 / 4;
 
+    // Raw source words of the next frame.  Slots that have nothing to load (outside the image, or beyond the footprint)
+    // stay zero for the whole loop: they are cleared once here and never written again.
     uint32_t u[3][3];
-    auto fetch = [&](const uint8_t* __restrict__ base) {
 #pragma unroll
-        for (int j = 0; j < 3; j++) {
-            u[j][0] = u[j][1] = u[j][2] = 0u;
-            if (j * kRectThreads < ngroups && soff[j] >= 0) {
-                const uint32_t* p = reinterpret_cast<const uint32_t*>(base + soff[j]);
-                u[j][0] = __ldg(p); u[j][1] = __ldg(p + 1); u[j][2] = __ldg(p + 2);
-            }
+    for (int j = 0; j < 3; j++) u[j][0] = u[j][1] = u[j][2] = 0u;
+    const bool third = ngroups > 2 * kRectThreads;                   // CTA-uniform: most footprints fit two slots per thread
+    auto fetch_slot = [&](const uint8_t* __restrict__ base, int j) {
+        if (soff[j] >= 0) {
+            const uint32_t* p = reinterpret_cast<const uint32_t*>(base + soff[j]);
+            u[j][0] = __ldg(p); u[j][1] = __ldg(p + 1); u[j][2] = __ldg(p + 2);
+        }
+    };
+    auto fetch = [&](const uint8_t* __restrict__ base) {
+        fetch_slot(base, 0);
+        fetch_slot(base, 1);
+        if (third) fetch_slot(base, 2);
+    };
+    auto store_slot = [&](uint32_t* buf, int j) {
+        const int g = tid + j * kRectThreads;
+        if (g < ngroups) {
+            uint4 o;
+            o.x = u[j][0];
+            o.y = __byte_perm(u[j][0], u[j][1], 0x4543);
+            o.z = __byte_perm(u[j][1], u[j][2], 0x4432);
+            o.w = u[j][2] >> 8;
+            *reinterpret_cast<uint4*>(&buf[g << 2]) = o;
         }
     };
     fetch(src);
 
     for (int f = f0; f < f1; f++) {
         uint32_t* const buf = s_src2[(f - f0) & 1];
-#pragma unroll
-        for (int j = 0; j < 3; j++) {
-            const int g = tid + j * kRectThreads;
-            if (g < ngroups) {
-                uint4 o;
-                o.x = u[j][0];
-                o.y = __byte_perm(u[j][0], u[j][1], 0x4543);
-                o.z = __byte_perm(u[j][1], u[j][2], 0x4432);
-                o.w = u[j][2] >> 8;
-                *reinterpret_cast<uint4*>(&buf[g << 2]) = o;
-            }
-        }
+        store_slot(buf, 0);
+        store_slot(buf, 1);
+        if (third) store_slot(buf, 2);
         __syncthreads();      // the only barrier of the iteration: the other buffer was last read before the previous one
         if (f + 1 < f1) { src += a.src_frame; fetch(src); }            // next frame's words fly during this frame's blend
 #if SA_BATCH_L2_PREFETCH
         if (f + 2 < f1) {                                               // and the frame after that is pulled into L2, so that
             const uint8_t* nxt = src + a.src_frame;                     // next iteration's fetch is an L2 hit, not a DRAM round trip
-#pragma unroll
-            for (int j = 0; j < 3; j++)
-                if (j * kRectThreads < ngroups && soff[j] >= 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(nxt + soff[j]));
+            if (soff[0] >= 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(nxt + soff[0]));
+            if (soff[1] >= 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(nxt + soff[1]));
+            if (third && soff[2] >= 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(nxt + soff[2]));
         }
 #endif
 
