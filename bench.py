@@ -218,6 +218,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--heatmap", action="store_true", help="include stage C in the step")
     ap.add_argument("--frame-fastest", type=int, default=-1)
+    ap.add_argument("--opt", action="append", default=[], help="library tuning option key=value (sa_set_option), repeatable")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     wname = args.workload
@@ -252,6 +253,9 @@ def main():
     g.set_calibration(calib)
     if args.frame_fastest >= 0:
         g.set_option("frame_fastest", args.frame_fastest)
+    for kv in args.opt:
+        k_, v_ = kv.split("=")
+        g.set_option(k_, int(v_))
     g.stub_disparity(n, seed=1234 + rank)
     g.synchronize()
 

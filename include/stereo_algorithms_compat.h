@@ -55,6 +55,10 @@ SA_API const char* sa_ref_LastError(void* p);
 SA_API int sa_ref_Heatmap(void* p, uint8_t* out_bgr);
 /* The demo's pointcloud.txt writer (FastACVNet_plus/test/main.cpp:62-69): one "x y z r g b" line per point. */
 SA_API int sa_write_pointcloud_txt(const char* path, const float* points, size_t n_points);
+/* Same points as a PLY file (the text dump is 50+ bytes per point): x y z as float, r g b as uchar,
+ * binary little-endian (binary != 0, 15 bytes per point) or ASCII.  skip_non_finite != 0 drops points whose x, y or z is
+ * inf/NaN (the dense cloud has them wherever the disparity is 0). */
+SA_API int sa_write_pointcloud_ply(const char* path, const float* points, size_t n_points, int binary, int skip_non_finite);
 
 #ifdef __cplusplus
 }

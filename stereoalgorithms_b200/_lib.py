@@ -88,6 +88,7 @@ SIGNATURES = {
     "sa_ref_LastError": (_cp, [_vp]),
     "sa_ref_Heatmap": (_i, [_vp, _vp]),
     "sa_write_pointcloud_txt": (_i, [_cp, _vp, _sz]),
+    "sa_write_pointcloud_ply": (_i, [_cp, _vp, _sz, _i, _i]),
 }
 
 _lib = None

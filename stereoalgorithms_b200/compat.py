@@ -119,3 +119,11 @@ def write_pointcloud_txt(path: str, pointcloud: np.ndarray) -> None:
     rc = L.load().sa_write_pointcloud_txt(path.encode(), pts.ctypes.data, pts.shape[0])
     if rc != 0:
         raise OSError(f"sa_write_pointcloud_txt({path}) failed with {rc}")
+
+
+def write_pointcloud_ply(path: str, pointcloud: np.ndarray, binary: bool = True, skip_non_finite: bool = True) -> None:
+    """x y z r g b points as a PLY file (binary little-endian by default)."""
+    pts = np.ascontiguousarray(pointcloud, np.float32).reshape(-1, 6)
+    rc = L.load().sa_write_pointcloud_ply(path.encode(), pts.ctypes.data, pts.shape[0], 1 if binary else 0, 1 if skip_non_finite else 0)
+    if rc != 0:
+        raise OSError(f"sa_write_pointcloud_ply({path}) failed with {rc}")

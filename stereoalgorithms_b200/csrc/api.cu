@@ -182,6 +182,7 @@ static int stage_rectify(sa_handle* h, int f0, int n, const uint8_t* src_l, cons
         a.force_generic = (int)h->opt_force_generic;
         a.persistent_ctas = (int)(h->opt_persistent > 0 ? h->opt_persistent * h->sm_count : 0);
         a.batch_loop = h->opt_batch_loop ? h->sm_count : 0;
+        a.batch_ctas_per_sm = (int)h->opt_batch_ctas;
         {
             StageScope t(h, SA_STAGE_RECTIFY, s);
             SA_CUDA(h, launch_rectify(a, s, &h->launches));
@@ -829,6 +830,7 @@ int sa_set_option(sa_handle* h, const char* key, long value)
     else if (!std::strcmp(key, "exact_div")) h->opt_exact_div = value;
     else if (!std::strcmp(key, "persistent")) h->opt_persistent = value;
     else if (!std::strcmp(key, "batch_loop")) h->opt_batch_loop = value;
+    else if (!std::strcmp(key, "batch_ctas")) h->opt_batch_ctas = value;
     else return fail(h, SA_ERR_INVALID_ARG, "sa_set_option: unknown key '%s'", key);
     return SA_OK;
 }

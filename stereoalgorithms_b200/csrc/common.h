@@ -100,6 +100,7 @@ struct sa_handle {
     long opt_force_generic = 0;
     long opt_exact_div = 0;
     long opt_persistent = 0;          // CTAs per SM of the persistent rectify kernel (0 = one CTA per tile, the default: measured faster)
+    long opt_batch_ctas = 16;         // frame chunking target of the batch kernel, CTAs per SM
     long opt_batch_loop = 1;          // rectify_batch_kernel (default); 0 = one CTA per (tile, eye, frame)
     int sm_count = 148;
 
@@ -158,6 +159,7 @@ struct RectifyArgs {
     int force_generic;                 // testing: never take the fast tile path
     int persistent_ctas;               // > 0: persistent pipelined kernel with this many CTAs (a multiple of the SM count)
     int batch_loop;                    // > 0 (= SM count): one CTA per (tile, eye) walks a run of frames (rectify_batch_kernel)
+    int batch_ctas_per_sm;             // target number of CTAs per SM for the frame chunking of the batch kernel
 };
 cudaError_t launch_rectify(const RectifyArgs& a, cudaStream_t s, long* launches);
 

@@ -203,4 +203,28 @@ int sa_write_pointcloud_txt(const char* path, const float* points, size_t n_poin
     return std::fclose(f) == 0 ? SA_OK : SA_ERR_IO;
 }
 
+int sa_write_pointcloud_ply(const char* path, const float* points, size_t n_points, int binary, int skip_non_finite)
+{
+    if (!path || !points) return SA_ERR_INVALID_ARG;
+    auto finite = [](float v) { return v == v && v - v == 0.0f; };
+    size_t kept = n_points;
+    if (skip_non_finite) {
+        kept = 0;
+        for (size_t i = 0; i < n_points; i++) kept += finite(points[i * 6]) && finite(points[i * 6 + 1]) && finite(points[i * 6 + 2]);
+    }
+    FILE* f = std::fopen(path, "wb");
+    if (!f) return SA_ERR_IO;
+    std::fprintf(f, "ply\nformat %s 1.0\ncomment StereoAlgorithms geometry path\nelement vertex %zu\n"
+                    "property float x\nproperty float y\nproperty float z\nproperty uchar red\nproperty uchar green\nproperty uchar blue\nend_header\n",
+                 binary ? "binary_little_endian" : "ascii", kept);
+    for (size_t i = 0; i < n_points; i++) {
+        const float* q = points + i * 6;
+        if (skip_non_finite && !(finite(q[0]) && finite(q[1]) && finite(q[2]))) continue;
+        const unsigned char c[3] = {(unsigned char)q[3], (unsigned char)q[4], (unsigned char)q[5]};
+        if (binary) { std::fwrite(q, sizeof(float), 3, f); std::fwrite(c, 1, 3, f); }
+        else std::fprintf(f, "%g %g %g %u %u %u\n", q[0], q[1], q[2], c[0], c[1], c[2]);
+    }
+    return std::fclose(f) == 0 ? SA_OK : SA_ERR_IO;
+}
+
 }  // extern "C"

@@ -447,14 +447,18 @@ __global__ void __launch_bounds__(kRectThreads, 4) rectify_persistent_kernel(con
 #ifndef SA_BATCH_L2_PREFETCH
 #define SA_BATCH_L2_PREFETCH 1
 #endif
-template <int DTYPE, bool IDENT, bool WRITE_TENSOR>
-__global__ void __launch_bounds__(kRectThreads, SA_BATCH_MINB) rectify_batch_kernel(const RectifyArgs a, int tiles_x, int out_align, int frames_per_cta)
+// A4: every input row and every rectified row starts on a 4-byte boundary and W is a multiple of 4 (640, 1920, 3840 ...).
+// !A4 (e.g. 1242-wide frames, whose rows and frames are only 2-byte aligned): source words are loaded from the enclosing
+// aligned words and funnel-shifted by the address's low bits, rectified bytes leave as byte stores.
+// PART: the tile reaches past the right/bottom image edge; its out-of-image pixels are masked.  Kept out of the common
+// instantiation: the extra predicates cost ~15 % there.
+template <int DTYPE, bool IDENT, bool WRITE_TENSOR, bool A4, bool PART>
+__device__ __forceinline__ void rectify_batch_body(const RectifyArgs& a, int tiles_x, int out_align, int frames_per_cta, uint32_t (*s_src2)[kFootprintWords],
+                                                   typename TensorT<DTYPE>::type* s_lut)
 {
     using T = typename TensorT<DTYPE>::type;
-    __shared__ __align__(16) uint32_t s_src2[2][kFootprintWords];   // double buffered: one barrier per frame
     uint32_t* const s_src = s_src2[0];
     uint32_t* const s_out = s_src2[1];                               // only the generic path needs s_out; it never overlaps the loop below
-    __shared__ T s_lut[IDENT ? 1 : 768];
 
     const int tid = threadIdx.x;
     const int W = a.W, H = a.H;
@@ -462,14 +466,17 @@ __global__ void __launch_bounds__(kRectThreads, SA_BATCH_MINB) rectify_batch_ker
     const int f0 = chunk * frames_per_cta, f1 = min(a.n, f0 + frames_per_cta);
     const int tx0 = blockIdx.x * kTileW, ty0 = blockIdx.y * kTileH;
     const TileInfo ti = a.tiles[eye][blockIdx.y * tiles_x + blockIdx.x];
-    if (!IDENT) {
-        const T* lut = static_cast<const T*>(a.lut);
-        for (int i = tid; i < 768; i += kRectThreads) s_lut[i] = lut[i];
+    bool fast = ti.w > 0;                                              // partial tiles at the right/bottom edge stay on this path, with their
+                                                                       // out-of-image pixels masked (pvalid below)
+    if (!A4) {
+        // the 16-byte aligned window around a misaligned group of 4 source pixels must not reach past the end of the
+        // buffer: only possible for the last group of the last image row, i.e. in the bottom-right tile(s)
+        if (ti.y0 + ti.h >= H && ti.x0 + ti.w >= W - 4) fast = false;
     }
-    if (!(ti.w > 0 && tx0 + kTileW <= W && ty0 + kTileH <= H)) {      // edge tile / unstaged footprint: generic path, frame by frame
+    if (!fast) {                                                      // edge tile / unstaged footprint: generic path, frame by frame
         for (int f = f0; f < f1; f++) {
             __syncthreads();
-            tile_generic<DTYPE, IDENT, WRITE_TENSOR, true>(a, ti, eye, f, tx0, ty0, out_align, s_src, s_out, s_lut);
+            tile_generic<DTYPE, IDENT, WRITE_TENSOR, A4>(a, ti, eye, f, tx0, ty0, out_align, s_src, s_out, s_lut);
         }
         return;
     }
@@ -477,12 +484,19 @@ __global__ void __launch_bounds__(kRectThreads, SA_BATCH_MINB) rectify_batch_ker
     // ---- per-calibration state of this thread (frame independent) ----------------------------------------------
     const int pix0 = (ty0 + (tid >> 6)) * W + tx0 + (tid & (kTileW - 1));
     const int rstep = 4 * W, wstep = 3 * W, plane = W * H;
+    uint32_t pvalid = 0xfu;             // bit k: pixel k of this thread lies inside the image
+    if (PART) {
+        pvalid = 0;
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+            if (tx0 + (tid & (kTileW - 1)) < W && ty0 + (tid >> 6) + 4 * k < H) pvalid |= 1u << k;
+    }
     uint32_t toff[4], twt[4];           // byte offset of the top-left tap in s_src; (32-fx, fx, 32-fy, fy) as four bytes
     {
         const uint32_t* __restrict__ tmap = a.tmap[eye] + pix0;
 #pragma unroll
         for (int k = 0; k < 4; k++) {
-            const uint32_t t = __ldg(tmap + k * rstep);
+            const uint32_t t = (!PART || ((pvalid >> k) & 1u)) ? __ldg(tmap + k * rstep) : 0u;
             const uint32_t fx = (t >> 12) & 31u, fy = (t >> 17) & 31u;
             toff[k] = (t & 0xfffu) << 2;
             twt[k] = (32u - fx) | (fx << 8) | ((32u - fy) << 16) | (fy << 24);
@@ -492,6 +506,7 @@ __global__ void __launch_bounds__(kRectThreads, SA_BATCH_MINB) rectify_batch_ker
     const int ngroups = (ti.w >> 2) * ti.h;
     const int pitch = (int)a.src_pitch;
     int soff[3];                        // byte offset of this thread's staging groups inside a frame; -1 = nothing to load
+    uint32_t gcut = 0;                  // !A4: 3 bits per slot, number of pixels of the group inside the image if it straddles x = W (else 0)
 #pragma unroll
     for (int j = 0; j < 3; j++) {
         const int g = tid + j * kRectThreads;
@@ -499,28 +514,42 @@ __global__ void __launch_bounds__(kRectThreads, SA_BATCH_MINB) rectify_batch_ker
         if (g < ngroups) {
             const int gw = ti.w >> 2;
             const int r = (int)(((uint32_t)g * ti.inv_gw) >> 20), c = g - r * gw;
-            const int yy = ti.y0 + r, xx = ti.x0 + 4 * c;             // x0 and W are multiples of 4: a group is all in or all out
-            if ((unsigned)yy < (unsigned)H && (unsigned)xx < (unsigned)W) soff[j] = yy * pitch + 3 * xx;
+            const int yy = ti.y0 + r, xx = ti.x0 + 4 * c;             // A4: x0 and W are multiples of 4, a group is all in or all out
+            if ((unsigned)yy < (unsigned)H && (unsigned)xx < (unsigned)W) {
+                soff[j] = yy * pitch + 3 * xx;
+                if (!A4 && xx + 4 > W) gcut |= (uint32_t)(W - xx) << (3 * j);
+            }
         }
     }
     const int m = tid & 3;
     uint32_t sel = m == 0 ? 0x4210u : (m == 1 ? 0x5421u : 0x6542u);
     asm volatile("" : "+r"(sel));       // keep it in a register: recomputing the selects inside the frame loop costs 5 instructions per pixel
     const uint8_t* __restrict__ src = a.src[eye] + (size_t)f0 * a.src_frame;
-    uint32_t* __restrict__ rp = reinterpret_cast<uint32_t*>(a.rect[eye] + (size_t)f0 * plane * 3) + (3 * ((pix0 - m) >> 2) + m);
+    uint32_t* __restrict__ rp = reinterpret_cast<uint32_t*>(a.rect[eye] + (size_t)f0 * plane * 3) + (3 * ((pix0 - m) >> 2) + m);   // A4
+    uint8_t* __restrict__ rb = a.rect[eye] + (size_t)f0 * plane * 3 + (size_t)pix0 * 3;                                              // !A4
     T* __restrict__ tp = WRITE_TENSOR ? static_cast<T*>(a.tensor[eye]) + (size_t)f0 * a.tensor_frame + pix0 : nullptr;
     const size_t rect_frame_words = (size_t)plane * 3 / 4;
 
     // Raw source words of the next frame.  Slots that have nothing to load (outside the image, or beyond the footprint)
     // stay zero for the whole loop: they are cleared once here and never written again.
-    uint32_t u[3][3];
+    uint32_t u[3][A4 ? 3 : 4];
+    uint32_t ualign = 0;                                              // !A4: low address bits of each slot's group, 2 bits per slot
 #pragma unroll
-    for (int j = 0; j < 3; j++) u[j][0] = u[j][1] = u[j][2] = 0u;
+    for (int j = 0; j < 3; j++) { u[j][0] = u[j][1] = u[j][2] = 0u; if (!A4) u[j][A4 ? 0 : 3] = 0u; }
     const bool third = ngroups > 2 * kRectThreads;                   // CTA-uniform: most footprints fit two slots per thread
     auto fetch_slot = [&](const uint8_t* __restrict__ base, int j) {
         if (soff[j] >= 0) {
-            const uint32_t* p = reinterpret_cast<const uint32_t*>(base + soff[j]);
-            u[j][0] = __ldg(p); u[j][1] = __ldg(p + 1); u[j][2] = __ldg(p + 2);
+            if (A4) {
+                const uint32_t* p = reinterpret_cast<const uint32_t*>(base + soff[j]);
+                u[j][0] = __ldg(p); u[j][1] = __ldg(p + 1); u[j][2] = __ldg(p + 2);
+            } else {
+                const uintptr_t A = reinterpret_cast<uintptr_t>(base + soff[j]);
+                const uint32_t al = (uint32_t)A & 3u;
+                const uint32_t* p = reinterpret_cast<const uint32_t*>(A - al);
+                u[j][0] = __ldg(p); u[j][1] = __ldg(p + 1); u[j][2] = __ldg(p + 2);
+                u[j][A4 ? 0 : 3] = al ? __ldg(p + 3) : 0u;
+                ualign = (ualign & ~(3u << (2 * j))) | (al << (2 * j));
+            }
         }
     };
     auto fetch = [&](const uint8_t* __restrict__ base) {
@@ -531,11 +560,22 @@ __global__ void __launch_bounds__(kRectThreads, SA_BATCH_MINB) rectify_batch_ker
     auto store_slot = [&](uint32_t* buf, int j) {
         const int g = tid + j * kRectThreads;
         if (g < ngroups) {
+            uint32_t w0 = u[j][0], w1 = u[j][1], w2 = u[j][2];
+            if (!A4) {
+                const uint32_t sh = ((ualign >> (2 * j)) & 3u) << 3;
+                w0 = __funnelshift_r(u[j][0], u[j][1], sh);
+                w1 = __funnelshift_r(u[j][1], u[j][2], sh);
+                w2 = __funnelshift_r(u[j][2], u[j][A4 ? 0 : 3], sh);
+            }
             uint4 o;
-            o.x = u[j][0];
-            o.y = __byte_perm(u[j][0], u[j][1], 0x4543);
-            o.z = __byte_perm(u[j][1], u[j][2], 0x4432);
-            o.w = u[j][2] >> 8;
+            o.x = w0;
+            o.y = __byte_perm(w0, w1, 0x4543);
+            o.z = __byte_perm(w1, w2, 0x4432);
+            o.w = w2 >> 8;
+            if (!A4) {                                                // pixels of a straddling group beyond x = W are border (zero)
+                const uint32_t nv = (gcut >> (3 * j)) & 7u;
+                if (nv) { if (nv < 2) o.y = 0u; if (nv < 3) o.z = 0u; o.w = 0u; }
+            }
             *reinterpret_cast<uint4*>(&buf[g << 2]) = o;
         }
     };
@@ -573,18 +613,39 @@ __global__ void __launch_bounds__(kRectThreads, SA_BATCH_MINB) rectify_batch_ker
             const uint32_t vB = __dp2a_hi(__byte_perm(tB, bB, 0x5410), wt, 512u) >> 10;
             const uint32_t vG = __dp2a_hi(__byte_perm(tG, bG, 0x5410), wt, 512u) >> 10;
             const uint32_t vR = __dp2a_hi(__byte_perm(tR, bR, 0x5410), wt, 512u) >> 10;
-            const uint32_t v = vB | (vG << 8) | (vR << 16);
-            const uint32_t nb = __shfl_down_sync(0xffffffffu, v, 1);
-            if (m < 3) rp[k * wstep] = __byte_perm(v, nb, sel);
-            if (WRITE_TENSOR) {
+            const bool pv = !PART || ((pvalid >> k) & 1u);             // W % 4 == 0 under A4: the 4 lanes of a packed group agree on it
+            if (A4) {
+                const uint32_t v = vB | (vG << 8) | (vR << 16);
+                const uint32_t nb = __shfl_down_sync(0xffffffffu, v, 1);
+                if (m < 3 && pv) rp[k * wstep] = __byte_perm(v, nb, sel);
+            } else if (pv) {
+                uint8_t* q = rb + (size_t)k * rstep * 3;
+                q[0] = (uint8_t)vB; q[1] = (uint8_t)vG; q[2] = (uint8_t)vR;
+            }
+            if (WRITE_TENSOR && pv) {
                 T r, g, b;
                 normalise<DTYPE, IDENT, T>(s_lut, vB, vG, vR, r, g, b);
                 tp[k * rstep] = r; tp[k * rstep + plane] = g; tp[k * rstep + 2 * plane] = b;
             }
         }
-        rp += rect_frame_words;
+        if (A4) rp += rect_frame_words; else rb += (size_t)plane * 3;
         if (WRITE_TENSOR) tp += a.tensor_frame;
     }
+}
+
+template <int DTYPE, bool IDENT, bool WRITE_TENSOR, bool A4>
+__global__ void __launch_bounds__(kRectThreads, SA_BATCH_MINB) rectify_batch_kernel(const RectifyArgs a, int tiles_x, int out_align, int frames_per_cta)
+{
+    using T = typename TensorT<DTYPE>::type;
+    __shared__ __align__(16) uint32_t s_src2[2][kFootprintWords];   // double buffered: one barrier per frame
+    __shared__ T s_lut[IDENT ? 1 : 768];
+    if (!IDENT) {
+        const T* lut = static_cast<const T*>(a.lut);
+        for (int i = threadIdx.x; i < 768; i += kRectThreads) s_lut[i] = lut[i];
+    }
+    const bool full = (int)(blockIdx.x + 1) * kTileW <= a.W && (int)(blockIdx.y + 1) * kTileH <= a.H;
+    if (full) rectify_batch_body<DTYPE, IDENT, WRITE_TENSOR, A4, false>(a, tiles_x, out_align, frames_per_cta, s_src2, s_lut);
+    else rectify_batch_body<DTYPE, IDENT, WRITE_TENSOR, A4, true>(a, tiles_x, out_align, frames_per_cta, s_src2, s_lut);
 }
 
 // rectify = 0 (images already rectified) and the tail of the resize path: BGR u8 -> normalised planes only.
@@ -621,17 +682,20 @@ inline bool lut_is_identity(int model) { return model == SA_MODEL_RAFTSTEREO || 
 template <int DTYPE, bool IDENT, bool WT>
 cudaError_t launch_rectify_t(const RectifyArgs& a, bool aligned4, int tiles_x, int out_align, int fast_ok, dim3 grid, cudaStream_t s)
 {
-    if (fast_ok && aligned4 && a.batch_loop) {
+    if (a.batch_loop && !a.force_generic && a.src_pitch * (size_t)a.H < (1u << 31) && (size_t)a.W * a.H * 3 < (1u << 30)) {
+        const bool a4 = fast_ok && aligned4;
         const int tiles_y = (a.H + kTileH - 1) / kTileH;
         // frames per CTA: enough CTAs for ~8 per SM slot (balance), as many frames per CTA as that allows (amortisation)
         const long long tile_eyes = (long long)tiles_x * tiles_y * 2;
-        long long want = a.batch_loop * 8LL;                         // a.batch_loop carries the SM count
+        long long want = (long long)a.batch_loop * (a.batch_ctas_per_sm > 0 ? a.batch_ctas_per_sm : 8);   // a.batch_loop carries the SM count
         int fpc = (int)((tile_eyes * a.n + want - 1) / want);
         if (fpc < 1) fpc = 1;
         if (fpc > a.n) fpc = a.n;
         const int chunks = (a.n + fpc - 1) / fpc;
         if (2 * chunks <= 65535) {
-            rectify_batch_kernel<DTYPE, IDENT, WT><<<dim3((unsigned)tiles_x, (unsigned)tiles_y, 2u * (unsigned)chunks), kRectThreads, 0, s>>>(a, tiles_x, out_align, fpc);
+            const dim3 g((unsigned)tiles_x, (unsigned)tiles_y, 2u * (unsigned)chunks);
+            if (a4) rectify_batch_kernel<DTYPE, IDENT, WT, true><<<g, kRectThreads, 0, s>>>(a, tiles_x, out_align, fpc);
+            else rectify_batch_kernel<DTYPE, IDENT, WT, false><<<g, kRectThreads, 0, s>>>(a, tiles_x, out_align, fpc);
             return cudaGetLastError();
         }
     }

@@ -85,7 +85,11 @@ __device__ __forceinline__ void point_xyz(const Q10& q, float d, float fc, float
 // (float) of byte k of a packed BGRx word without the conversion unit: 2^23 + byte, exactly, minus 2^23
 __device__ __forceinline__ float byte_to_float(uint32_t c, uint32_t sel) { return __uint_as_float(__byte_perm(c, 0x4b000000u, sel)) - 8388608.0f; }
 
-// Loads disparity + colour of the thread's 4 pixels.  VEC: everything 16/4-byte aligned and contiguous.
+// Loads disparity + colour of the thread's 4 pixels.
+//   VEC: disparity 16-byte aligned, colour rows contiguous and 4-byte aligned -> one float4 + three words.
+//   !VEC: scalar disparity loads; colour from the enclosing aligned words, funnel-shifted by the frame's misalignment
+//   (e.g. 1242x375 frames start on 2-byte boundaries), as long as the rows are contiguous and the 16-byte window stays
+//   inside the frame; the last pixels of a frame and pitched images fall back to byte loads.
 template <bool VEC>
 __device__ __forceinline__ void load4(const ReprojectArgs& a, int frame, int p0, int npix, int row0, int col0, float d[4], uint32_t c[4])
 {
@@ -101,6 +105,15 @@ __device__ __forceinline__ void load4(const ReprojectArgs& a, int frame, int p0,
         } else {
             d[0] = d[1] = d[2] = d[3] = 0.f; c[0] = c[1] = c[2] = c[3] = 0u;
         }
+    } else if (a.color_pitch == (size_t)a.w * 3 && p0 + 8 <= npix) {
+#pragma unroll
+        for (int k = 0; k < 4; k++) d[k] = disp[p0 + k];
+        const uintptr_t A = reinterpret_cast<uintptr_t>(color + (size_t)p0 * 3);
+        const uint32_t al = (uint32_t)A & 3u, sh = al << 3;
+        const uint32_t* cp = reinterpret_cast<const uint32_t*>(A - al);
+        const uint32_t r0 = __ldg(cp), r1 = __ldg(cp + 1), r2 = __ldg(cp + 2), r3 = __ldg(cp + 3);   // cp + 3 is inside the frame: p0 + 8 <= npix
+        const uint32_t u0 = __funnelshift_r(r0, r1, sh), u1 = __funnelshift_r(r1, r2, sh), u2 = __funnelshift_r(r2, r3, sh);
+        c[0] = u0; c[1] = __byte_perm(u0, u1, 0x4543); c[2] = __byte_perm(u1, u2, 0x4432); c[3] = u2 >> 8;
     } else {
         int row = row0, col = col0;
 #pragma unroll
@@ -167,7 +180,8 @@ __global__ void __launch_bounds__(kThreads) reduce_minmax_kernel(const unsigned*
     }
 }
 
-template <bool VEC, bool FAST>
+// VEC: aligned inputs (see load4).  VOUT: every frame of the point buffer starts on a 16-byte boundary.
+template <bool VEC, bool VOUT, bool FAST>
 __global__ void __launch_bounds__(kThreads) reproject_dense_kernel(const ReprojectArgs a)
 {
     __shared__ __align__(16) float4 s_pts[kThreads / 32][192];
@@ -208,7 +222,7 @@ __global__ void __launch_bounds__(kThreads) reproject_dense_kernel(const Reproje
 
     float* out = a.points + (size_t)frame * npix * 6;
     const size_t warp_px0 = (size_t)(blockIdx.x * kThreads + warp * 32) * 4;
-    if (VEC) {
+    if (VOUT) {
         float4* out4 = reinterpret_cast<float4*>(out) + warp_px0 * 6 / 4;
         const size_t lim = ((size_t)npix * 6 / 4 > warp_px0 * 6 / 4) ? (size_t)npix * 6 / 4 - warp_px0 * 6 / 4 : 0;
 #pragma unroll
@@ -216,6 +230,7 @@ __global__ void __launch_bounds__(kThreads) reproject_dense_kernel(const Reproje
             const int s = lane + 32 * m;
             if ((size_t)s < lim) out4[s] = sw[s ^ ((s / 24) & 1)];
         }
+
     } else {
         const float* sf = reinterpret_cast<const float*>(sw);
         float* o = out + warp_px0 * 6;
@@ -371,6 +386,8 @@ cudaError_t launch_reproject(const ReprojectArgs& a, cudaStream_t s, long* launc
     // the shared-reciprocal quotient needs bounded, finite numerators: |Q entry| <= 2^20 and image sides <= 2^14
     bool fast = !a.exact_div && a.w <= 16384 && a.h <= 16384;
     for (int i : {0, 1, 3, 4, 5, 7, 8, 9, 11}) fast = fast && (fabsf(a.q[i]) <= 1048576.0f);   // false for NaN too
+    // point rows leave as 16-byte stores when every frame of the point buffer starts on a 16-byte boundary (even pixel count)
+    const bool vout = (npix % 2 == 0) && (((uintptr_t)a.points) % 16 == 0);
     dim3 grid((unsigned)nblk, (unsigned)a.n);
 #define SA_DISPATCH(KERNEL, ...)                                                                         \
     do {                                                                                                 \
@@ -378,7 +395,11 @@ cudaError_t launch_reproject(const ReprojectArgs& a, cudaStream_t s, long* launc
         else { if (fast) KERNEL<false, true><<<grid, kThreads, 0, s>>>(__VA_ARGS__); else KERNEL<false, false><<<grid, kThreads, 0, s>>>(__VA_ARGS__); }   \
     } while (0)
     if (!a.compact) {
-        SA_DISPATCH(reproject_dense_kernel, a);
+#define SA_DENSE(V, O, F) reproject_dense_kernel<V, O, F><<<grid, kThreads, 0, s>>>(a)
+        if (vec) { if (fast) SA_DENSE(true, true, true); else SA_DENSE(true, true, false); }
+        else if (vout) { if (fast) SA_DENSE(false, true, true); else SA_DENSE(false, true, false); }
+        else { if (fast) SA_DENSE(false, false, true); else SA_DENSE(false, false, false); }
+#undef SA_DENSE
         if (launches) ++*launches;
         if (a.counts) { fill_int_kernel<<<(a.n + 255) / 256, 256, 0, s>>>(a.counts, a.n, (int)npix); if (launches) ++*launches; }
         return cudaGetLastError();

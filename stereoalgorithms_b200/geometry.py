@@ -132,6 +132,18 @@ class StereoGeometry:
         self._check(self._lib.sa_rectify_preprocess(self._h, n, pl, pr, pitch, DEVICE if dev_l else HOST, 1 if rectify else 0, stream))
         return n
 
+    def rectify_preprocess_side_by_side(self, frames, rectify: bool = True, stream=None):
+        """frames: uint8 [n, H, 2W, 3], left half | right half - the 1280x480 capture the reference's 3-argument
+        RectifyImage overload splits with two clone()s (FastACVNet_plus/src/FastACVNet_plus_Algorithm.cpp:116-131).
+        Zero copy here: the two eyes are the same buffer at a byte offset of 3*W with a row pitch of 6*W."""
+        p, dev = _ptr(frames)
+        n = int(frames.shape[0])
+        if tuple(frames.shape[1:]) != (self.H, 2 * self.W, 3):
+            raise ValueError(f"expected [n, {self.H}, {2 * self.W}, 3], got {tuple(frames.shape)}")
+        # consecutive frames are 6*W*H bytes apart = H rows of the doubled pitch, which is what the C ABI assumes
+        self._check(self._lib.sa_rectify_preprocess(self._h, n, p, p + 3 * self.W, 6 * self.W, DEVICE if dev else HOST, 1 if rectify else 0, stream))
+        return n
+
     def input_tensor_ptr(self, eye: int = LEFT) -> int:
         return int(self._lib.sa_input_tensor(self._h, eye))
 

@@ -413,3 +413,20 @@ def test_reproject_special_disparities(calibs):
             wc, k, _ = O.reproject_compact(O.HITNET, d[0, 0], img, c["Q"])
             assert cc[0] == k
             assert_close_points(cp[0, :k], wc, "special values compact")
+
+
+def test_side_by_side_capture_frame(calibs, demo_pair):
+    """the 1280x480 side-by-side capture, split by pitch/offset instead of two clone()s."""
+    import torch
+    c = calibs["calib_b"]
+    l, r = demo_pair
+    sbs = np.ascontiguousarray(np.concatenate([l, r], axis=1))[None]          # [1, 480, 1280, 3]
+    sbs = np.concatenate([sbs, sbs[:, ::-1]], 0)                               # second frame: upside down
+    with geom(640, 480, model="FastACVNet_plus", max_batch=2) as g:
+        g.set_calibration(c)
+        for frames in (sbs, torch.from_numpy(sbs).cuda()):                     # host and device resident
+            g.rectify_preprocess_side_by_side(frames)
+            for i in range(2):
+                li, ri = sbs[i, :, :640], sbs[i, :, 640:]
+                rl, rr = O.rectify_pair(c, np.ascontiguousarray(li), np.ascontiguousarray(ri))
+                assert np.array_equal(g.rectified(2, 0)[i], rl) and np.array_equal(g.rectified(2, 1)[i], rr)

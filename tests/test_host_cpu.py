@@ -151,3 +151,19 @@ def test_product_does_not_import_the_oracle():
             if f.endswith((".py", ".cu", ".cpp", ".h")):
                 text = open(os.path.join(root, f)).read()
                 assert "oracle" not in text.lower(), f"{f} mentions the oracle"
+
+
+def test_pointcloud_ply_writer(lib, tmp_path):
+    pts = np.array([[1.5, -0.25, 2.0, 255, 0, 12], [np.inf, 1, 1, 1, 2, 3], [0.5, 0.25, np.nan, 9, 9, 9], [3, 4, 5, 7, 8, 9]], np.float32)
+    b = str(tmp_path / "cloud.ply")
+    assert lib.sa_write_pointcloud_ply(b.encode(), pts.ctypes.data, len(pts), 1, 1) == 0
+    raw = open(b, "rb").read()
+    head, body = raw.split(b"end_header\n", 1)
+    assert b"format binary_little_endian 1.0" in head and b"element vertex 2\n" in head and b"property uchar blue" in head
+    rec = np.frombuffer(body, dtype=np.dtype([("xyz", "<f4", 3), ("rgb", "u1", 3)]))
+    assert len(rec) == 2
+    assert np.array_equal(rec["xyz"], pts[[0, 3], :3]) and np.array_equal(rec["rgb"], pts[[0, 3], 3:].astype(np.uint8))
+    a = str(tmp_path / "cloud_ascii.ply")
+    assert lib.sa_write_pointcloud_ply(a.encode(), pts.ctypes.data, len(pts), 0, 0) == 0
+    lines = open(a).read().split("end_header\n")[1].splitlines()
+    assert len(lines) == 4 and lines[0] == "1.5 -0.25 2 255 0 12" and lines[3] == "3 4 5 7 8 9"
