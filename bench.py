@@ -38,6 +38,8 @@ UNIT = "pairs/s"
 # BASELINE.json configs (index -> workload).  configs[1] is the one the metric is quoted on at N=1.
 WORKLOADS = {
     "raft_realtime_640x480_b64_f16": dict(model="RAFTStereo", W=640, H=480, batch=64, dtype="f16", calib=("calib_a", 1.0)),
+    "fastacv_640x480_b64_f32": dict(model="FastACVNet_plus", W=640, H=480, batch=64, dtype="f32", calib=("calib_a", 1.0)),
+    "hitnet_640x480_b64_f32": dict(model="HitNet", W=640, H=480, batch=64, dtype="f32", calib=("calib_b", 1.0)),
     "fastacv_kitti_1242x375_b256_f32": dict(model="FastACVNet_plus", W=1242, H=375, batch=256, dtype="f32", calib=("calib_a", 1242 / 640)),
     "stream_1080p_b64_f32": dict(model="FastACVNet_plus", W=1920, H=1080, batch=64, dtype="f32", calib=("calib_a", 3.0)),
     "uhd_2160p_b16_f32": dict(model="FastACVNet_plus", W=3840, H=2160, batch=16, dtype="f32", calib=("calib_a", 6.0)),

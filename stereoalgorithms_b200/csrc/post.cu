@@ -8,7 +8,9 @@ namespace sa {
 
 namespace {
 
-__constant__ uint32_t c_jet[256] = {
+// in global memory, not __constant__: each CTA copies it to shared memory with one coalesced load per thread (a
+// constant-bank read indexed by threadIdx serialises 32 ways)
+__device__ const uint32_t c_jet[256] = {
 #include "jet_lut.inc"
 };
 

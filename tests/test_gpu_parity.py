@@ -430,3 +430,27 @@ def test_side_by_side_capture_frame(calibs, demo_pair):
                 li, ri = sbs[i, :, :640], sbs[i, :, 640:]
                 rl, rr = O.rectify_pair(c, np.ascontiguousarray(li), np.ascontiguousarray(ri))
                 assert np.array_equal(g.rectified(2, 0)[i], rl) and np.array_equal(g.rectified(2, 1)[i], rr)
+
+
+@pytest.mark.parametrize("ctas_per_sm", [1, 16, 1000])
+def test_rectified_long_batches_all_chunkings(calibs, demo_pair, ctas_per_sm):
+    """The batch-loop kernel with many frames per CTA (register prefetch of f+1, L2 prefetch of f+2, both shared-memory
+    buffers in rotation), with the default chunking, and with one frame per CTA; tensors checked too."""
+    c = calibs["calib_c_rational"]                       # strong rotation: large footprints, some tiles unstaged
+    n = 37
+    rng = np.random.default_rng(5)
+    L = np.stack([np.roll(demo_pair[0], int(rng.integers(0, 640)), axis=1) for _ in range(n)])
+    R = np.stack([np.roll(demo_pair[1], int(rng.integers(0, 480)), axis=0) for _ in range(n)])
+    (l1, l2), (r1, r2) = O.rectify_maps(c, (640, 480))
+    lut = O.norm_lut(O.FASTACVNET_PLUS)
+    with geom(640, 480, model="FastACVNet_plus", max_batch=n) as g:
+        g.set_option("batch_ctas", ctas_per_sm)
+        g.set_calibration(c)
+        g.rectify_preprocess(L, R)
+        gl, gr, tl = g.rectified(n, 0), g.rectified(n, 1), g.tensor(n, 0)
+        for i in range(n):
+            wl = OC.remap(L[i], l1, l2)
+            assert np.array_equal(gl[i], wl), i
+            assert np.array_equal(gr[i], OC.remap(R[i], r1, r2)), i
+            if i % 6 == 0:
+                assert np.array_equal(tl[i], np.stack([lut[ch][wl[..., 2 - ch]] for ch in range(3)]))
