@@ -168,6 +168,14 @@ typedef struct sa_calibration {
     int nD_l, nD_r;
 } sa_calibration;
 SA_API int sa_parse_calibration_yaml(const char* path, sa_calibration* out, char* err, size_t err_len);
+/* The writing half of the calibration format (Stereo_Calibration/Stereo_Calibration.cpp:165-179 writes it with
+ * cv::FileStorage): "%YAML:1.0", "---", then one !!opencv-matrix node per matrix, doubles printed so that they read back
+ * bit-identically.  sa_scale_calibration derives the calibration of a resized / cropped camera from an existing one
+ * (done by hand in the reference's harnesses): rows 0-1 of K_l, K_r, P1, P2 are multiplied by
+ * `scale`, (crop_x, crop_y) pixels are subtracted from the principal points, and Q is rebuilt to match
+ * (Q[3] = -cx', Q[7] = -cy', Q[11] = f', Q[15] *= scale; Q[14] = -1/Tx is unchanged).  in == out is allowed. */
+SA_API int sa_write_calibration_yaml(const char* path, const sa_calibration* c);
+SA_API int sa_scale_calibration(const sa_calibration* in, double scale, double crop_x, double crop_y, sa_calibration* out);
 SA_API int sa_norm_lut(int model, float* lut768);
 SA_API int sa_resize_table(int dst, int src, int* table);
 

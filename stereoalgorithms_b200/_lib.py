@@ -68,6 +68,8 @@ SIGNATURES = {
     "sa_set_engine": (_i, [_vp, ENGINE_FN, _vp]),
     "sa_run_batch": (_i, [_vp, _i, _vp, _vp, _i, _u, _vp, _vp, _vp, _vp, _vp]),
     "sa_parse_calibration_yaml": (_i, [_cp, C.POINTER(sa_calibration), C.c_char_p, _sz]),
+    "sa_write_calibration_yaml": (_i, [_cp, C.POINTER(sa_calibration)]),
+    "sa_scale_calibration": (_i, [C.POINTER(sa_calibration), C.c_double, C.c_double, C.c_double, C.POINTER(sa_calibration)]),
     "sa_norm_lut": (_i, [_i, _vp]),
     "sa_resize_table": (_i, [_i, _i, _vp]),
     "sa_reproject_compact_noalloc": (_i, [_vp, _sz, _vp, _sz, _sz, _vp, _i, _i, _i, _i, _vp, _vp, _vp, C.c_char_p, _sz]),

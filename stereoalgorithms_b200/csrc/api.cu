@@ -465,6 +465,64 @@ int sa_parse_calibration_yaml(const char* path, sa_calibration* out, char* err, 
     return SA_OK;
 }
 
+int sa_write_calibration_yaml(const char* path, const sa_calibration* c)
+{
+    if (!path || !c) return SA_ERR_INVALID_ARG;
+    if (c->nD_l < 0 || c->nD_l > 14 || c->nD_r < 0 || c->nD_r > 14) return SA_ERR_INVALID_ARG;
+    FILE* f = std::fopen(path, "w");
+    if (!f) return SA_ERR_IO;
+    std::fprintf(f, "%%YAML:1.0\n---\n");
+    auto node = [&](const char* name, int rows, int cols, const double* d) {
+        std::fprintf(f, "%s: !!opencv-matrix\n   rows: %d\n   cols: %d\n   dt: d\n   data: [ ", name, rows, cols);
+        int col = 11;
+        for (int i = 0; i < rows * cols; i++) {
+            char buf[40];
+            int len;
+            if (d[i] == (double)(long long)d[i] && std::fabs(d[i]) < 1e15) len = std::snprintf(buf, sizeof buf, "%lld.", (long long)d[i]);   // "0." "1." like OpenCV
+            else len = std::snprintf(buf, sizeof buf, "%.17g", d[i]);
+            if (col + len + 2 > 78) { std::fprintf(f, "\n       "); col = 7; }
+            std::fprintf(f, "%s%s", buf, i + 1 < rows * cols ? ", " : " ]\n");
+            col += len + 2;
+        }
+    };
+    node("intrinsic_left", 3, 3, c->K_l);
+    node("distCoeffs_left", 1, c->nD_l, c->D_l);
+    node("intrinsic_right", 3, 3, c->K_r);
+    node("distCoeffs_right", 1, c->nD_r, c->D_r);
+    node("R", 3, 3, c->R);
+    node("T", 3, 1, c->T);
+    node("R_L", 3, 3, c->R_L);
+    node("R_R", 3, 3, c->R_R);
+    node("P1", 3, 4, c->P1);
+    node("P2", 3, 4, c->P2);
+    node("Q", 4, 4, c->Q);
+    return std::fclose(f) == 0 ? SA_OK : SA_ERR_IO;
+}
+
+int sa_scale_calibration(const sa_calibration* in, double scale, double crop_x, double crop_y, sa_calibration* out)
+{
+    if (!in || !out || !(scale > 0.0)) return SA_ERR_INVALID_ARG;
+    sa_calibration c = *in;
+    double* k33[2] = {c.K_l, c.K_r};
+    for (double* K : k33) {
+        for (int i = 0; i < 6; i++) K[i] *= scale;       // rows 0 and 1
+        K[2] -= crop_x;
+        K[5] -= crop_y;
+    }
+    double* p34[2] = {c.P1, c.P2};
+    for (double* P : p34) {
+        for (int i = 0; i < 8; i++) P[i] *= scale;
+        P[2] -= crop_x;
+        P[6] -= crop_y;
+    }
+    c.Q[3] = -c.P1[2];
+    c.Q[7] = -c.P1[6];
+    c.Q[11] = c.P1[0];
+    c.Q[15] *= scale;
+    *out = c;
+    return SA_OK;
+}
+
 int sa_norm_lut(int model, float* lut768)
 {
     if (!lut768 || model < 0 || model > 3) return SA_ERR_INVALID_ARG;

@@ -167,3 +167,33 @@ def test_pointcloud_ply_writer(lib, tmp_path):
     assert lib.sa_write_pointcloud_ply(a.encode(), pts.ctypes.data, len(pts), 0, 0) == 0
     lines = open(a).read().split("end_header\n")[1].splitlines()
     assert len(lines) == 4 and lines[0] == "1.5 -0.25 2 255 0 12" and lines[3] == "3 4 5 7 8 9"
+
+
+@pytest.mark.parametrize("name", ["calib_a", "calib_c_rational"])
+def test_calibration_writer_round_trip_and_scaling(lib, name, tmp_path):
+    from stereoalgorithms_b200._lib import sa_calibration
+    src = os.path.join(GOLDEN, name + ".yml")
+    rc, c, err = _parse(lib, src)
+    assert rc == 0, err
+    out = str(tmp_path / "rewritten.yml")
+    assert lib.sa_write_calibration_yaml(out.encode(), C.byref(c)) == 0
+    # both parsers read it back bit-identically, and it is in the reference's format
+    rc, c2, err = _parse(lib, out)
+    assert rc == 0, err
+    assert bytes(c) == bytes(c2)
+    want, back = O.load_calibration_yaml(src), O.load_calibration_yaml(out)
+    for k in O.CALIB_KEYS:
+        assert np.array_equal(want[k].ravel(), back[k].ravel()), k
+    assert open(out).read().startswith("%YAML:1.0\n---\nintrinsic_left: !!opencv-matrix\n   rows: 3\n   cols: 3\n   dt: d\n   data: [ ")
+    cv2 = pytest.importorskip("cv2")                       # and cv::FileStorage itself accepts it
+    fs = cv2.FileStorage(out, cv2.FILE_STORAGE_READ)
+    assert np.array_equal(fs.getNode("Q").mat(), want["Q"]) and np.array_equal(fs.getNode("distCoeffs_right").mat().ravel(), want["distCoeffs_right"].ravel())
+    fs.release()
+    # scaling: the KITTI-size and 1080p calibrations of the benchmark configs
+    for s, cy in ((1242 / 640, (480 * 1242 / 640 - 375) / 2), (3.0, 180.0)):
+        sc = sa_calibration()
+        assert lib.sa_scale_calibration(C.byref(c), s, 0.0, cy, C.byref(sc)) == 0
+        ref = O.scale_calibration(want, s, crop_y=cy)
+        for f, k in {"K_l": "intrinsic_left", "K_r": "intrinsic_right", "P1": "P1", "P2": "P2", "Q": "Q", "R_L": "R_L"}.items():
+            assert np.array_equal(np.array(getattr(sc, f)), ref[k].ravel()), (s, k)
+    assert lib.sa_scale_calibration(C.byref(c), -1.0, 0.0, 0.0, C.byref(sc)) != 0
