@@ -454,3 +454,40 @@ def test_rectified_long_batches_all_chunkings(calibs, demo_pair, ctas_per_sm):
             assert np.array_equal(gr[i], OC.remap(R[i], r1, r2)), i
             if i % 6 == 0:
                 assert np.array_equal(tl[i], np.stack([lut[ch][wl[..., 2 - ch]] for ch in range(3)]))
+
+
+def test_engine_callback_sits_between_the_two_halves(calibs, demo_pair):
+    """sa_set_engine: the slot of context->enqueueV3(stream) (TRTFastACVNet_plus.cpp:152).  The callback gets the device
+    tensors of its chunk and the disparity slot, on the library's stream; here it checks the tensors it is handed and
+    copies a prepared 'network output' into place with a stream-ordered device-to-device copy."""
+    import torch
+    from cuda.bindings import runtime as rt
+    c = calibs["calib_a"]
+    n, W, H = 7, 640, 480
+    L = np.stack([np.roll(demo_pair[0], 11 * i, axis=1) for i in range(n)])
+    R = np.stack([np.roll(demo_pair[1], 11 * i, axis=1) for i in range(n)])
+    D = np.stack([O.synthetic_disparity(W, H, 300 + i) for i in range(n)])
+    net_out = torch.from_numpy(D).cuda()
+    calls = []
+
+    def engine(stream, first_frame, m, left_tensor, right_tensor, disparity):
+        calls.append((first_frame, m, left_tensor, right_tensor))
+        src = net_out.data_ptr() + first_frame * W * H * 4
+        (err,) = rt.cudaMemcpyAsync(disparity, src, m * W * H * 4, rt.cudaMemcpyKind.cudaMemcpyDeviceToDevice, stream)
+        return 0 if err == rt.cudaError_t.cudaSuccess else 1
+
+    pts = np.zeros((n, W * H, 6), np.float32)
+    disp = np.zeros((n, H, W), np.float32)
+    with geom(W, H, model="FastACVNet_plus", max_batch=8) as g:
+        g.set_calibration(c)
+        g.set_option("chunk", 3)
+        g.set_engine(engine)
+        g.run_batch(L, R, n, rectify=True, stub_seed=0, pointcloud=pts, disparity=disp)
+        assert [(f, m) for f, m, _, _ in calls] == [(0, 3), (3, 3), (6, 1)]
+        t0 = g.input_tensor_ptr(0)
+        assert calls[1][2] == t0 + 3 * 3 * W * H * 4 and calls[1][3] == g.input_tensor_ptr(1) + 3 * 3 * W * H * 4
+        assert np.array_equal(disp, D)
+        for i in (0, 4, 6):
+            ref = O.run_pair(O.FASTACVNET_PLUS, c, L[i], R[i], D[i])
+            assert_close_points(pts[i], ref["points"], f"engine frame {i}")
+        g.set_engine(None)
