@@ -131,6 +131,28 @@ class ClockSampler:
                 "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def bind_to_gpu_numa_node(gpu_index):
+    """Pin this process to the CPUs of the NUMA node the GPU hangs off, so that the pinned host buffers of the end-to-end
+    leg are allocated next to the GPU's PCIe root (matters with several ranks on a two-socket box).  Best effort."""
+    try:
+        bdf = subprocess.check_output(["nvidia-smi", "--query-gpu=pci.bus_id", "--format=csv,noheader", "-i", str(gpu_index)], text=True).strip().lower()
+        bdf = bdf[-12:] if len(bdf) > 12 else bdf                      # 00000000:1B:00.0 -> 0000:1b:00.0
+        node = int(open(f"/sys/bus/pci/devices/{bdf}/numa_node").read())
+        if node < 0:
+            return None
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return node
+    except Exception:
+        pass
+    return None
+
+
 def measured_hbm_peak():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -243,8 +265,12 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product has no CPU path (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
+    numa = bind_to_gpu_numa_node(local) if world > 1 else None
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        # The data path has no collective (frames share nothing): the process group only carries the barrier around the timed
+        # region and two scalar reductions (MAX of the elapsed time, SUM of the pairs), so gloo over loopback is enough and
+        # keeps NCCL's start-up (and its version banner on stdout) out of a run that never moves data between GPUs.
+        dist.init_process_group("gloo")
     n = wl["batch"]
     W, H = wl["W"], wl["H"]
     calib = load_calib(wl)
@@ -372,6 +398,7 @@ def main():
                 "dtype": "u8 fixed-point + f32 (%s tensors)" % wl["dtype"], "data": "synthetic",
                 "config": {"workload": wname, "model": wl["model"], "size": [W, H], "pairs_per_gpu_per_step": n, "tensor_dtype": wl["dtype"],
                            "reproject": "dense", "heatmap": bool(args.heatmap), "parallelism": f"frame-sharded x{world}, no collective",
+                           "numa_node_rank0": numa,
                            "l2": "working set per step %.0f MB >> 126 MB L2 (no flush needed)" % (bytes_per_pair(wl, "total") * n / 1e6),
                            "network_slot": "synthetic disparity written once before timing (RAFTStereo: its sign alternates per step, same work)"},
                 "kernel_ms_per_step": 1e3 * dev_s / args.steps, "host_ms_per_step": 1e3 * elapsed / args.steps,
