@@ -93,8 +93,19 @@ static void inv3(const double a[9], double t[9])
 static int tiles_x(const sa_handle* h) { return (h->W + kTileW - 1) / kTileW; }
 static int tiles_y(const sa_handle* h) { return (h->H + kTileH - 1) / kTileH; }
 
+// Largest staged footprint over both eyes: the box of the TMA rectify path.  Recomputed from the tile tables that exist.
+static int refresh_box(sa_handle* h)
+{
+    int mx[2] = {0, 0};
+    SA_CUDA(h, cudaMemcpy(mx, h->fp_max, sizeof mx, cudaMemcpyDeviceToHost));
+    h->box_w = mx[0];
+    h->box_h = mx[1];
+    return SA_OK;
+}
+
 static int compute_maps(sa_handle* h)
 {
+    SA_CUDA(h, cudaMemsetAsync(h->fp_max, 0, 2 * sizeof(int), h->stream));
     for (int eye = 0; eye < 2; eye++) {
         MapParams p{};
         double A[9];
@@ -108,13 +119,13 @@ static int compute_maps(sa_handle* h)
         {
             StageScope t(h, SA_STAGE_MAPS, h->stream);
             SA_CUDA(h, launch_init_maps(p, h->W, h->H, h->map1[eye], h->map2[eye], h->stream));
-            SA_CUDA(h, launch_tile_info(h->map1[eye], h->map2[eye], h->W, h->H, h->tiles[eye], h->tmap[eye], tiles_x(h), tiles_y(h), (int)h->opt_force_direct, h->stream));
+            SA_CUDA(h, launch_tile_info(h->map1[eye], h->map2[eye], h->W, h->H, h->tiles[eye], h->tmap[eye], h->fp_max, tiles_x(h), tiles_y(h), (int)h->opt_force_direct, h->stream));
             h->launches += 2;
         }
         h->have_maps[eye] = true;
     }
     SA_CUDA(h, cudaStreamSynchronize(h->stream));
-    return SA_OK;
+    return refresh_box(h);
 }
 
 static int set_q(sa_handle* h, const double* Q)
@@ -183,6 +194,8 @@ static int stage_rectify(sa_handle* h, int f0, int n, const uint8_t* src_l, cons
         a.persistent_ctas = (int)(h->opt_persistent > 0 ? h->opt_persistent * h->sm_count : 0);
         a.batch_loop = h->opt_batch_loop ? h->sm_count : 0;
         a.batch_ctas_per_sm = (int)h->opt_batch_ctas;
+        a.bulk_copy = (int)h->opt_bulk;
+        a.box_w = h->box_w; a.box_h = h->box_h;
         {
             StageScope t(h, SA_STAGE_RECTIFY, s);
             SA_CUDA(h, launch_rectify(a, s, &h->launches));
@@ -344,6 +357,8 @@ int sa_create(const sa_config* cfg, sa_handle** out)
     if (!(cfg->flags & SA_FLAG_NO_POINT_BUF)) A(dev_alloc(&h->points, N * npix * 6));
     if (!(cfg->flags & SA_FLAG_NO_HEATMAP_BUF)) A(dev_alloc(&h->heat, N * npix * 3));
     A(dev_alloc(&h->counts, N));
+    A(dev_alloc(&h->fp_max, 2));
+    if (ok) A(cudaMemset(h->fp_max, 0, 2 * sizeof(int)));
     A(dev_alloc(&h->minmax, N * 2));
     A(dev_alloc(&h->blk_counts, N * nblk));
     A(dev_alloc(&h->blk_offsets, N * nblk));
@@ -390,7 +405,7 @@ int sa_destroy(sa_handle* h)
         cudaFree(h->raw[e]); cudaFree(h->rect[e]); cudaFree(h->net_u8[e]); cudaFree(h->map1[e]); cudaFree(h->map2[e]); cudaFree(h->tiles[e]); cudaFree(h->tmap[e]);
     }
     cudaFree(h->tensor[0]); cudaFree(h->disp); cudaFree(h->points); cudaFree(h->heat); cudaFree(h->counts); cudaFree(h->minmax);
-    cudaFree(h->blk_counts); cudaFree(h->blk_offsets); cudaFree(h->blk_minmax); cudaFree(h->lut32); cudaFree(h->lut16); cudaFree(h->rs_x); cudaFree(h->rs_y);
+    cudaFree(h->fp_max); cudaFree(h->blk_counts); cudaFree(h->blk_offsets); cudaFree(h->blk_minmax); cudaFree(h->lut32); cudaFree(h->lut16); cudaFree(h->rs_x); cudaFree(h->rs_y);
     for (int s = 0; s < SA_STAGE_COUNT_; s++) {
         for (auto ev : h->timer.begin[s]) cudaEventDestroy(ev);
         for (auto ev : h->timer.end[s]) cudaEventDestroy(ev);
@@ -571,11 +586,11 @@ int sa_set_maps(sa_handle* h, int eye, const int16_t* map1, const uint16_t* map2
     const size_t mpix = (size_t)h->W * h->H;
     SA_CUDA(h, cudaMemcpyAsync(h->map1[eye], map1, mpix * 4, cudaMemcpyHostToDevice, h->stream));
     SA_CUDA(h, cudaMemcpyAsync(h->map2[eye], map2, mpix * 2, cudaMemcpyHostToDevice, h->stream));
-    SA_CUDA(h, launch_tile_info(h->map1[eye], h->map2[eye], h->W, h->H, h->tiles[eye], h->tmap[eye], tiles_x(h), tiles_y(h), (int)h->opt_force_direct, h->stream));
+    SA_CUDA(h, launch_tile_info(h->map1[eye], h->map2[eye], h->W, h->H, h->tiles[eye], h->tmap[eye], h->fp_max, tiles_x(h), tiles_y(h), (int)h->opt_force_direct, h->stream));
     h->launches += 1;
     SA_CUDA(h, cudaStreamSynchronize(h->stream));
     h->have_maps[eye] = true;
-    return SA_OK;
+    return refresh_box(h);      // fp_max only grows here (the other eye's table may be older): a larger box is always valid
 }
 
 int sa_get_maps(sa_handle* h, int eye, int16_t* map1, uint16_t* map2)
@@ -889,6 +904,7 @@ int sa_set_option(sa_handle* h, const char* key, long value)
     else if (!std::strcmp(key, "persistent")) h->opt_persistent = value;
     else if (!std::strcmp(key, "batch_loop")) h->opt_batch_loop = value;
     else if (!std::strcmp(key, "batch_ctas")) h->opt_batch_ctas = value;
+    else if (!std::strcmp(key, "bulk")) h->opt_bulk = value;
     else return fail(h, SA_ERR_INVALID_ARG, "sa_set_option: unknown key '%s'", key);
     return SA_OK;
 }

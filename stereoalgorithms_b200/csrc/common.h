@@ -75,6 +75,8 @@ struct sa_handle {
     uint16_t* map2[2] = {nullptr, nullptr};
     sa::TileInfo* tiles[2] = {nullptr, nullptr};
     uint32_t* tmap[2] = {nullptr, nullptr};   // derived per-pixel table of the fast rectify path, [H][W]
+    int* fp_max = nullptr;                    // device: {max footprint width, height} over staged full tiles of both eyes
+    int box_w = 0, box_h = 0;                 // host copy of fp_max
     float* lut32 = nullptr;                   // [3][256]
     __half* lut16 = nullptr;
     unsigned* minmax = nullptr;               // [N][2] ordered-uint encodings (min, ~max)
@@ -101,6 +103,7 @@ struct sa_handle {
     long opt_exact_div = 0;
     long opt_persistent = 0;          // CTAs per SM of the persistent rectify kernel (0 = one CTA per tile, the default: measured faster)
     long opt_batch_ctas = 16;         // frame chunking target of the batch kernel, CTAs per SM
+    long opt_bulk = 0;                // rectify_tma_kernel when the frames are 16-byte aligned
     long opt_batch_loop = 1;          // rectify_batch_kernel (default); 0 = one CTA per (tile, eye, frame)
     int sm_count = 148;
 
@@ -138,8 +141,8 @@ int parse_opencv_yaml(const char* path, std::vector<YamlMat>& out, std::string& 
 
 // kernels (each returns a cudaError_t from the launch)
 cudaError_t launch_init_maps(const MapParams& p, int W, int H, int* map1, uint16_t* map2, cudaStream_t s);
-cudaError_t launch_tile_info(const int* map1, const uint16_t* map2, int W, int H, TileInfo* tiles, uint32_t* tmap, int tiles_x, int tiles_y, int force_direct,
-                             cudaStream_t s);
+cudaError_t launch_tile_info(const int* map1, const uint16_t* map2, int W, int H, TileInfo* tiles, uint32_t* tmap, int* fp_max, int tiles_x, int tiles_y,
+                             int force_direct, cudaStream_t s);
 
 struct RectifyArgs {
     const uint8_t* src[2];
@@ -159,6 +162,8 @@ struct RectifyArgs {
     int force_generic;                 // testing: never take the fast tile path
     int persistent_ctas;               // > 0: persistent pipelined kernel with this many CTAs (a multiple of the SM count)
     int batch_loop;                    // > 0 (= SM count): one CTA per (tile, eye) walks a run of frames (rectify_batch_kernel)
+    int bulk_copy;                     // 1: stage the footprints with TMA tensor copies + mbarriers (rectify_tma_kernel) when alignment allows
+    int box_w, box_h;                  // largest staged footprint of the calibration over full tiles (pixels, rows), both eyes
     int batch_ctas_per_sm;             // target number of CTAs per SM for the frame chunking of the batch kernel
 };
 cudaError_t launch_rectify(const RectifyArgs& a, cudaStream_t s, long* launches);

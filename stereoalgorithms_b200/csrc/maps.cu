@@ -56,7 +56,8 @@ cudaError_t launch_init_maps(const MapParams& p, int W, int H, int* map1, uint16
 
 // One CTA per output tile: min/max of the (clamped) integer source coordinates of its pixels.
 __global__ void __launch_bounds__(256) tile_info_kernel(const int* __restrict__ map1, const uint16_t* __restrict__ map2, int W, int H,
-                                                        TileInfo* __restrict__ tiles, uint32_t* __restrict__ tmap, int tiles_x, int force_direct)
+                                                        TileInfo* __restrict__ tiles, uint32_t* __restrict__ tmap, int* __restrict__ fp_max, int tiles_x,
+                                                        int force_direct)
 {
     __shared__ TileInfo s_t;
     const int tile = blockIdx.x;
@@ -99,6 +100,7 @@ __global__ void __launch_bounds__(256) tile_info_kernel(const int* __restrict__ 
             const uint32_t gw = (uint32_t)w >> 2;
             t.inv_gw = ((1u << 20) + gw - 1) / gw;
             if (x0 >= 0 && ymin >= 0 && x0 + w <= W && ymin + h <= H) t.flags |= kTileInterior;
+            if (fp_max && tx0 + kTileW <= W && ty0 + kTileH <= H) { atomicMax(fp_max, w); atomicMax(fp_max + 1, h); }   // box of the TMA path
         }
         tiles[tile] = t;
         s_t = t;
@@ -123,10 +125,10 @@ __global__ void __launch_bounds__(256) tile_info_kernel(const int* __restrict__ 
     }
 }
 
-cudaError_t launch_tile_info(const int* map1, const uint16_t* map2, int W, int H, TileInfo* tiles, uint32_t* tmap, int tiles_x, int tiles_y, int force_direct,
-                             cudaStream_t s)
+cudaError_t launch_tile_info(const int* map1, const uint16_t* map2, int W, int H, TileInfo* tiles, uint32_t* tmap, int* fp_max, int tiles_x, int tiles_y,
+                             int force_direct, cudaStream_t s)
 {
-    tile_info_kernel<<<tiles_x * tiles_y, 256, 0, s>>>(map1, map2, W, H, tiles, tmap, tiles_x, force_direct);
+    tile_info_kernel<<<tiles_x * tiles_y, 256, 0, s>>>(map1, map2, W, H, tiles, tmap, fp_max, tiles_x, force_direct);
     return cudaGetLastError();
 }
 

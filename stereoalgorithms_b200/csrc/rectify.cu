@@ -16,6 +16,8 @@
 //   4. the normalised RGB planes go straight to global memory (a warp writes 32 consecutive floats/halves of a
 //      plane row); the rectified BGR bytes of four neighbouring lanes are packed into three words with one
 //      shuffle + byte-permute and leave as 96-byte coalesced row segments (edge tiles: through shared memory).
+#include <cuda.h>   // CUtensorMap and its enums only; the one driver function used is fetched with cudaGetDriverEntryPoint
+
 #include "common.h"
 
 #ifndef SA_BLEND_DP4A
@@ -653,6 +655,199 @@ __global__ void __launch_bounds__(kRectThreads, SA_BATCH_MINB) rectify_batch_ker
     else rectify_batch_body<DTYPE, IDENT, WRITE_TENSOR, A4, true>(a, tiles_x, out_align, frames_per_cta, s_src2, s_lut);
 }
 
+// ---- TMA variant: the footprint arrives as ONE tensor copy per frame, an mbarrier ring orders producer and consumers ------
+// Same work decomposition as rectify_batch_kernel (one CTA per (tile, eye), a run of frames), but the staging is done by
+// the Tensor Memory Accelerator: the source batch is described once per launch by a 3-D tensor map over 4-byte words
+// (3W/4 words x H rows x n frames, byte strides = row pitch and frame size), and for every frame ONE elected thread issues
+// ONE cp.async.bulk.tensor.3d for a box of (bw words x bh rows x 1 frame) at the tile's footprint origin, completing on an
+// mbarrier.  The box is the largest footprint of the calibration; whatever part of it lies outside the image - negative
+// coordinates included - is zero-filled by the hardware, which is exactly BORDER_CONSTANT 0.  Three raw (packed BGR)
+// stages are in flight: frames f+1 and f+2 travel while frame f is blended.  No thread spends instructions or registers
+// on loads, there is no __syncthreads in the frame loop (warps wait on / arrive at the mbarriers of the ring), and the
+// taps are read straight from the packed rows: three aligned words per row and two funnel shifts give the six bytes of a
+// horizontal tap pair at any byte offset.
+// Requirements on top of A4: source base, row pitch and frame size multiples of 16 bytes.
+// (Bulk and tensor copies need a 16-byte aligned global start; a footprint origin is only a multiple of 4 pixels = 12 bytes,
+// so the box starts at the origin rounded down to 16 pixels.  tools/exp/tma_test.cu is the micro-test that pinned this down.)
+constexpr int kTmaStages = 3;
+constexpr int kTmaStageBytes = 12288;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* tm, int c0, int c1, int c2, uint64_t* bar)
+{
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(smem_u32(dst)),
+                 "l"(tm), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+template <int DTYPE, bool IDENT, bool WRITE_TENSOR>
+__global__ void __launch_bounds__(kRectThreads, 4)
+    rectify_tma_kernel(const RectifyArgs a, const __grid_constant__ CUtensorMap tm_left, const __grid_constant__ CUtensorMap tm_right, int tiles_x, int out_align,
+                       int frames_per_cta, int bw, int bh)
+{
+    using T = typename TensorT<DTYPE>::type;
+    __shared__ __align__(128) uint32_t s_raw[kTmaStages][kTmaStageBytes / 4];   // packed BGR boxes, bw words per row
+    __shared__ __align__(8) uint64_t s_full[kTmaStages], s_empty[kTmaStages];
+    __shared__ T s_lut[IDENT ? 1 : 768];
+
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int W = a.W, H = a.H;
+    const int eye = blockIdx.z & 1, chunk = blockIdx.z >> 1;
+    const int f0 = chunk * frames_per_cta, f1 = min(a.n, f0 + frames_per_cta);
+    const int tx0 = blockIdx.x * kTileW, ty0 = blockIdx.y * kTileH;
+    const TileInfo ti = a.tiles[eye][blockIdx.y * tiles_x + blockIdx.x];
+    if (!IDENT) {
+        const T* lut = static_cast<const T*>(a.lut);
+        for (int i = tid; i < 768; i += kRectThreads) s_lut[i] = lut[i];
+    }
+    const int rowb = bw * 4;                                             // bytes per row of a staged box
+    // the box must cover the footprint (+ the third word every tap pair reads); it does for every staged full tile
+    // The innermost coordinate of a tensor copy must be a multiple of 16 bytes: the box starts at the footprint origin
+    // rounded down to 16 pixels (48 bytes), xpad pixels left of it.
+    const int xpad = ti.x0 & 15;
+    const bool fast = ti.w > 0 && tx0 + kTileW <= W && ty0 + kTileH <= H && 3 * (ti.w + xpad) + 8 <= rowb && ti.h <= bh;
+    if (!fast) {   // edge tile / unstaged or oversized footprint: generic path, frame by frame (s_raw doubles as its scratch)
+        for (int f = f0; f < f1; f++) {
+            __syncthreads();
+            tile_generic<DTYPE, IDENT, WRITE_TENSOR, true>(a, ti, eye, f, tx0, ty0, out_align, s_raw[0], s_raw[1], s_lut);
+        }
+        return;
+    }
+    if (tid == 0) {
+        for (int st = 0; st < kTmaStages; st++) { mbar_init(&s_full[st], 1); mbar_init(&s_empty[st], kRectThreads / 32); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    const int pix0 = (ty0 + (tid >> 6)) * W + tx0 + (tid & (kTileW - 1));
+    const int rstep = 4 * W, wstep = 3 * W, plane = W * H;
+    uint32_t toff[4], twt[4];           // byte offset of the top-left tap pair inside a staged box (low 2 bits = byte shift); weights
+    {
+        const uint32_t* __restrict__ tmap = a.tmap[eye] + pix0;
+        const uint32_t fw = (uint32_t)ti.w;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const uint32_t t = __ldg(tmap + k * rstep);
+            const uint32_t fx = (t >> 12) & 31u, fy = (t >> 17) & 31u, off = t & 0xfffu;
+            const uint32_t ry = off / fw, rx = off - ry * fw;
+            toff[k] = ry * (uint32_t)rowb + 3u * (rx + (uint32_t)xpad);
+            twt[k] = (32u - fx) | (fx << 8) | ((32u - fy) << 16) | (fy << 24);
+        }
+    }
+    const CUtensorMap* tm = eye ? &tm_right : &tm_left;
+    const int cx = 3 * ((ti.x0 - xpad) >> 2), cy = ti.y0;                 // box origin: word column (a multiple of 12 words = 48 bytes), row
+    const uint32_t stage_tx = (uint32_t)(rowb * bh);
+    const int m = tid & 3;
+    uint32_t sel = m == 0 ? 0x4210u : (m == 1 ? 0x5421u : 0x6542u);
+    asm volatile("" : "+r"(sel));
+    uint32_t* __restrict__ rp = reinterpret_cast<uint32_t*>(a.rect[eye] + (size_t)f0 * plane * 3) + (3 * ((pix0 - m) >> 2) + m);
+    T* __restrict__ tp = WRITE_TENSOR ? static_cast<T*>(a.tensor[eye]) + (size_t)f0 * a.tensor_frame + pix0 : nullptr;
+    const size_t rect_frame_words = (size_t)plane * 3 / 4;
+    const int nf = f1 - f0;
+    const int roww = bw;                                                // words per staged row
+
+    if (tid == 0) {
+        mbar_expect_tx(&s_full[0], stage_tx);
+        tma_load_3d(s_raw[0], tm, cx, cy, f0, &s_full[0]);
+        if (nf > 1) {
+            mbar_expect_tx(&s_full[1], stage_tx);
+            tma_load_3d(s_raw[1], tm, cx, cy, f0 + 1, &s_full[1]);
+        }
+    }
+    for (int i = 0; i < nf; i++) {
+        const int st = i % kTmaStages;
+        // refill the stage that was consumed in the previous iteration with frame i + 2
+        if (tid == 0 && i + 2 < nf) {
+            const int st2 = (i + 2) % kTmaStages;
+            if (i >= 1) mbar_wait(&s_empty[st2], (uint32_t)(((i - 1) / kTmaStages) & 1));
+            mbar_expect_tx(&s_full[st2], stage_tx);
+            tma_load_3d(s_raw[st2], tm, cx, cy, f0 + i + 2, &s_full[st2]);
+        }
+        __syncwarp();
+        mbar_wait(&s_full[st], (uint32_t)((i / kTmaStages) & 1));
+
+        const uint32_t* sw = s_raw[st];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const uint32_t sh = (toff[k] & 3u) << 3;
+            const uint32_t* p = sw + (toff[k] >> 2);
+            const uint32_t* q = p + roww;
+            const uint32_t a0 = p[0], a1 = p[1], a2 = p[2];
+            const uint32_t b0 = q[0], b1 = q[1], b2 = q[2];
+            // six bytes of the tap pair: lo = B0 G0 R0 B1, hi = G1 R1 . .
+            const uint32_t tlo = __funnelshift_r(a0, a1, sh), thi = __funnelshift_r(a1, a2, sh);
+            const uint32_t blo = __funnelshift_r(b0, b1, sh), bhi = __funnelshift_r(b1, b2, sh);
+            const uint32_t wt = twt[k];
+            const uint32_t wx = wt & 0xffffu, wxh = wt << 16;
+            const uint32_t tBG = __byte_perm(tlo, thi, 0x4130), tRR = __byte_perm(tlo, thi, 0x5252);
+            const uint32_t bBG = __byte_perm(blo, bhi, 0x4130), bRR = __byte_perm(blo, bhi, 0x5252);
+            const uint32_t tB = __dp4a(tBG, wx, 0u), tG = __dp4a(tBG, wxh, 0u), tR = __dp4a(tRR, wx, 0u);
+            const uint32_t bB = __dp4a(bBG, wx, 0u), bG = __dp4a(bBG, wxh, 0u), bR = __dp4a(bRR, wx, 0u);
+            const uint32_t vB = __dp2a_hi(__byte_perm(tB, bB, 0x5410), wt, 512u) >> 10;
+            const uint32_t vG = __dp2a_hi(__byte_perm(tG, bG, 0x5410), wt, 512u) >> 10;
+            const uint32_t vR = __dp2a_hi(__byte_perm(tR, bR, 0x5410), wt, 512u) >> 10;
+            const uint32_t v = vB | (vG << 8) | (vR << 16);
+            const uint32_t nb = __shfl_down_sync(0xffffffffu, v, 1);
+            if (m < 3) rp[k * wstep] = __byte_perm(v, nb, sel);
+            if (WRITE_TENSOR) {
+                T r, g, b;
+                normalise<DTYPE, IDENT, T>(s_lut, vB, vG, vR, r, g, b);
+                tp[k * rstep] = r; tp[k * rstep + plane] = g; tp[k * rstep + 2 * plane] = b;
+            }
+        }
+        rp += rect_frame_words;
+        if (WRITE_TENSOR) tp += a.tensor_frame;
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&s_empty[st]);                       // this warp is done reading the stage
+    }
+}
+
+// Encodes the 3-D tensor map of one eye's source batch.  The driver entry point is looked up once (no link-time libcuda).
+static bool encode_source_map(CUtensorMap* tm, const uint8_t* base, int W, int H, int n, size_t pitch, size_t frame, int bw, int bh)
+{
+    typedef CUresult (*encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static encode_fn fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess) fn = (encode_fn)p;
+    }
+    if (!fn) return false;
+    const cuuint64_t dims[3] = {(cuuint64_t)(3 * W / 4), (cuuint64_t)H, (cuuint64_t)n};
+    const cuuint64_t strides[2] = {(cuuint64_t)pitch, (cuuint64_t)frame};
+    const cuuint32_t box[3] = {(cuuint32_t)bw, (cuuint32_t)bh, 1u};
+    const cuuint32_t estr[3] = {1u, 1u, 1u};
+    return fn(tm, CU_TENSOR_MAP_DATA_TYPE_UINT32, 3, const_cast<uint8_t*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+              CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 // rectify = 0 (images already rectified) and the tail of the resize path: BGR u8 -> normalised planes only.
 template <int DTYPE, bool IDENT>
 __global__ void __launch_bounds__(256) preprocess_kernel(const PreprocArgs a)
@@ -699,6 +894,19 @@ cudaError_t launch_rectify_t(const RectifyArgs& a, bool aligned4, int tiles_x, i
         const int chunks = (a.n + fpc - 1) / fpc;
         if (2 * chunks <= 65535) {
             const dim3 g((unsigned)tiles_x, (unsigned)tiles_y, 2u * (unsigned)chunks);
+            // TMA staging: box = largest footprint of the calibration + up to 12 pixels of origin alignment, rows padded to 16 bytes
+            // plus the word the last tap pair over-reads
+            const int bw = ((3 * (a.box_w + 12) + 8 + 15) / 16) * 4, bh = a.box_h;
+            const bool tma_ok = a4 && a.bulk_copy && a.box_w > 0 && bw <= 256 && bh <= 256 && bw * 4 * bh <= kTmaStageBytes && a.src_pitch % 16 == 0 &&
+                                a.src_frame % 16 == 0 && ((uintptr_t)a.src[0] | (uintptr_t)a.src[1]) % 16 == 0;
+            if (tma_ok) {
+                CUtensorMap tl, tr;
+                if (encode_source_map(&tl, a.src[0], a.W, a.H, a.n, a.src_pitch, a.src_frame, bw, bh) &&
+                    encode_source_map(&tr, a.src[1], a.W, a.H, a.n, a.src_pitch, a.src_frame, bw, bh)) {
+                    rectify_tma_kernel<DTYPE, IDENT, WT><<<g, kRectThreads, 0, s>>>(a, tl, tr, tiles_x, out_align, fpc, bw, bh);
+                    return cudaGetLastError();
+                }
+            }
             if (a4) rectify_batch_kernel<DTYPE, IDENT, WT, true><<<g, kRectThreads, 0, s>>>(a, tiles_x, out_align, fpc);
             else rectify_batch_kernel<DTYPE, IDENT, WT, false><<<g, kRectThreads, 0, s>>>(a, tiles_x, out_align, fpc);
             return cudaGetLastError();

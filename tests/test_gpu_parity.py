@@ -81,7 +81,7 @@ def test_maps_absurd_calibrations(golden, calibs, tag):
 
 # ---- a3: rectified images -------------------------------------------------------------------------------------
 @pytest.mark.parametrize("name", ["calib_a", "calib_b", "calib_c_rational"])
-@pytest.mark.parametrize("variant", ["default", "tile_fastest", "force_direct", "force_generic", "persistent", "persistent_tile_fastest", "per_tile_cta"])
+@pytest.mark.parametrize("variant", ["default", "tile_fastest", "force_direct", "force_generic", "persistent", "persistent_tile_fastest", "per_tile_cta", "no_bulk"])
 def test_rectified_demo_bit_exact(golden, demo_pair, name, variant):
     g_ = golden["cases"]["demo_" + name]
     l, r = demo_pair
@@ -95,6 +95,8 @@ def test_rectified_demo_bit_exact(golden, demo_pair, name, variant):
             g.set_option("persistent", 4)
         if variant in ("per_tile_cta", "tile_fastest", "force_generic"):
             g.set_option("batch_loop", 0)
+        if variant == "no_bulk":
+            g.set_option("bulk", 0)
         if variant == "force_generic":
             g.set_option("force_generic", 1)
         g.load_calibration_yaml(os.path.join(GOLDEN, name + ".yml"))
@@ -108,10 +110,11 @@ def test_rectified_scaled_bit_exact(golden, calibs, name):
     g_ = golden["cases"]["scaled_" + name]
     c, (W, H) = scaled_case(calibs, name)
     li, ri = O.synthetic_image(W, H, g_["image_seeds"][0]), O.synthetic_image(W, H, g_["image_seeds"][1])
-    for batch_loop, persistent in ((1, 0), (0, 4), (0, 0)):
+    for batch_loop, persistent, bulk in ((1, 0, 1), (1, 0, 0), (0, 4, 0), (0, 0, 0)):
         with geom(W, H, model="CREStereo") as g:
             g.set_option("batch_loop", batch_loop)
             g.set_option("persistent", persistent)
+            g.set_option("bulk", bulk)
             g.set_calibration(c)
             g.rectify_preprocess(li[None], ri[None])
             assert md5(g.rectified(1, 0)[0]) == g_["rect_left"], name
@@ -433,7 +436,8 @@ def test_side_by_side_capture_frame(calibs, demo_pair):
 
 
 @pytest.mark.parametrize("ctas_per_sm", [1, 16, 1000])
-def test_rectified_long_batches_all_chunkings(calibs, demo_pair, ctas_per_sm):
+@pytest.mark.parametrize("bulk", [1, 0])
+def test_rectified_long_batches_all_chunkings(calibs, demo_pair, ctas_per_sm, bulk):
     """The batch-loop kernel with many frames per CTA (register prefetch of f+1, L2 prefetch of f+2, both shared-memory
     buffers in rotation), with the default chunking, and with one frame per CTA; tensors checked too."""
     c = calibs["calib_c_rational"]                       # strong rotation: large footprints, some tiles unstaged
@@ -445,6 +449,7 @@ def test_rectified_long_batches_all_chunkings(calibs, demo_pair, ctas_per_sm):
     lut = O.norm_lut(O.FASTACVNET_PLUS)
     with geom(640, 480, model="FastACVNet_plus", max_batch=n) as g:
         g.set_option("batch_ctas", ctas_per_sm)
+        g.set_option("bulk", bulk)
         g.set_calibration(c)
         g.rectify_preprocess(L, R)
         gl, gr, tl = g.rectified(n, 0), g.rectified(n, 1), g.tensor(n, 0)
