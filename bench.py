@@ -44,6 +44,12 @@ WORKLOADS = {
     "stream_1080p_b64_f32": dict(model="FastACVNet_plus", W=1920, H=1080, batch=64, dtype="f32", calib=("calib_a", 3.0)),
     "uhd_2160p_b16_f32": dict(model="FastACVNet_plus", W=3840, H=2160, batch=16, dtype="f32", calib=("calib_a", 6.0)),
 }
+# not BASELINE configs: diagnostic shapes used while tuning the 2-byte-aligned (W % 4 != 0) path
+WORKLOADS.update({
+    "exp_1240x375_b256_f32": dict(model="FastACVNet_plus", W=1240, H=375, batch=256, dtype="f32", calib=("calib_a", 1240 / 640)),
+    "exp_1242x375_b64_f32": dict(model="FastACVNet_plus", W=1242, H=375, batch=64, dtype="f32", calib=("calib_a", 1242 / 640)),
+    "exp_1242x376_b256_f32": dict(model="FastACVNet_plus", W=1242, H=376, batch=256, dtype="f32", calib=("calib_a", 1242 / 640)),
+})
 DEFAULT_WORKLOAD = "raft_realtime_640x480_b64_f16"
 
 

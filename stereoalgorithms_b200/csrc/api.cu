@@ -195,6 +195,8 @@ static int stage_rectify(sa_handle* h, int f0, int n, const uint8_t* src_l, cons
         a.batch_loop = h->opt_batch_loop ? h->sm_count : 0;
         a.batch_ctas_per_sm = (int)h->opt_batch_ctas;
         a.bulk_copy = (int)h->opt_bulk;
+        a.l2_prefetch = (int)h->opt_l2_prefetch;
+        a.force_unaligned = (int)h->opt_force_unaligned;
         a.box_w = h->box_w; a.box_h = h->box_h;
         {
             StageScope t(h, SA_STAGE_RECTIFY, s);
@@ -905,6 +907,8 @@ int sa_set_option(sa_handle* h, const char* key, long value)
     else if (!std::strcmp(key, "batch_loop")) h->opt_batch_loop = value;
     else if (!std::strcmp(key, "batch_ctas")) h->opt_batch_ctas = value;
     else if (!std::strcmp(key, "bulk")) h->opt_bulk = value;
+    else if (!std::strcmp(key, "force_unaligned")) h->opt_force_unaligned = value;
+    else if (!std::strcmp(key, "l2_prefetch")) h->opt_l2_prefetch = value;
     else return fail(h, SA_ERR_INVALID_ARG, "sa_set_option: unknown key '%s'", key);
     return SA_OK;
 }

@@ -446,9 +446,7 @@ __global__ void __launch_bounds__(kRectThreads, 4) rectify_persistent_kernel(con
 #ifndef SA_BATCH_MINB
 #define SA_BATCH_MINB 4
 #endif
-#ifndef SA_BATCH_L2_PREFETCH
-#define SA_BATCH_L2_PREFETCH 1
-#endif
+
 // A4: every input row and every rectified row starts on a 4-byte boundary and W is a multiple of 4 (640, 1920, 3840 ...).
 // !A4 (e.g. 1242-wide frames, whose rows and frames are only 2-byte aligned): source words are loaded from the enclosing
 // aligned words and funnel-shifted by the address's low bits, rectified bytes leave as byte stores.
@@ -465,15 +463,23 @@ __device__ __forceinline__ void rectify_batch_body(const RectifyArgs& a, int til
     const int tid = threadIdx.x;
     const int W = a.W, H = a.H;
     const int eye = blockIdx.z & 1, chunk = blockIdx.z >> 1;
-    const int f0 = chunk * frames_per_cta, f1 = min(a.n, f0 + frames_per_cta);
+    const int f0 = chunk * frames_per_cta;
+    int f1 = min(a.n, f0 + frames_per_cta);
     const int tx0 = blockIdx.x * kTileW, ty0 = blockIdx.y * kTileH;
     const TileInfo ti = a.tiles[eye][blockIdx.y * tiles_x + blockIdx.x];
-    bool fast = ti.w > 0;                                              // partial tiles at the right/bottom edge stay on this path, with their
+    const bool fast = ti.w > 0;                                        // partial tiles at the right/bottom edge stay on this path, with their
                                                                        // out-of-image pixels masked (pvalid below)
-    if (!A4) {
-        // the 16-byte aligned window around a misaligned group of 4 source pixels must not reach past the end of the
-        // buffer: only possible for the last group of the last image row, i.e. in the bottom-right tile(s)
-        if (ti.y0 + ti.h >= H && ti.x0 + ti.w >= W - 4) fast = false;
+    // !A4: a group of 4 source pixels that straddles x = W is loaded whole, i.e. up to 9 bytes past the end of its row.
+    // In the last image row that runs into the next frame - harmless - except in the LAST frame of the batch, where it
+    // would leave the caller's buffer.  Tiles whose footprint holds that group (the bottom-right one or two) therefore
+    // take the bounds-checked path for that one frame only.  (An earlier version sent them down the generic path for
+    // every frame: ~50x the work per frame, and with 85 frames per CTA the tail of the whole launch.)
+    if (!A4 && fast && ti.y0 + ti.h >= H && ti.x0 + ti.w >= W - 4 && f1 == a.n) {
+        f1--;
+        __syncthreads();
+        tile_generic<DTYPE, IDENT, WRITE_TENSOR, A4>(a, ti, eye, f1, tx0, ty0, out_align, s_src, s_out, s_lut);
+        __syncthreads();
+        if (f0 >= f1) return;
     }
     if (!fast) {                                                      // edge tile / unstaged footprint: generic path, frame by frame
         for (int f = f0; f < f1; f++) {
@@ -582,6 +588,8 @@ __device__ __forceinline__ void rectify_batch_body(const RectifyArgs& a, int til
         }
     };
     fetch(src);
+    // frames ahead (0 = off); automatic: 2, but off on the 2-byte-aligned path (measured 3 % slower there, 9 % faster elsewhere)
+    const int pfd = a.l2_prefetch >= 0 ? a.l2_prefetch : (A4 ? 2 : 0);
 
     for (int f = f0; f < f1; f++) {
         uint32_t* const buf = s_src2[(f - f0) & 1];
@@ -590,17 +598,12 @@ __device__ __forceinline__ void rectify_batch_body(const RectifyArgs& a, int til
         if (third) store_slot(buf, 2);
         __syncthreads();      // the only barrier of the iteration: the other buffer was last read before the previous one
         if (f + 1 < f1) { src += a.src_frame; fetch(src); }            // next frame's words fly during this frame's blend
-#if SA_BATCH_L2_PREFETCH
-#ifndef SA_BATCH_PF_DIST
-#define SA_BATCH_PF_DIST 2
-#endif
-        if (f + SA_BATCH_PF_DIST < f1) {                                // and a later frame is pulled into L2, so that
-            const uint8_t* nxt = src + (size_t)(SA_BATCH_PF_DIST - 1) * a.src_frame;   // its fetch is an L2 hit, not a DRAM round trip
+        if (pfd && f + pfd < f1) {                                      // and a later frame is pulled into L2, so that
+            const uint8_t* nxt = src + (size_t)(pfd - 1) * a.src_frame;   // its fetch is an L2 hit, not a DRAM round trip
             if (soff[0] >= 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(nxt + soff[0]));
             if (soff[1] >= 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(nxt + soff[1]));
             if (third && soff[2] >= 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(nxt + soff[2]));
         }
-#endif
 
         const char* sb = reinterpret_cast<const char*>(buf);
 #pragma unroll
@@ -624,8 +627,11 @@ __device__ __forceinline__ void rectify_batch_body(const RectifyArgs& a, int til
                 const uint32_t nb = __shfl_down_sync(0xffffffffu, v, 1);
                 if (m < 3 && pv) rp[k * wstep] = __byte_perm(v, nb, sel);
             } else if (pv) {
-                // byte stores: a word-packed variant for 2-byte aligned rows (lane roles rotated by the row's misalignment)
-                // was tried and measured slower (1.58 vs 1.47 ms on 256 pairs of 1242x375)
+                // Byte stores.  Two word-packed variants were tried and both measured SLOWER on 256 pairs of 1242x375 (rows
+                // only 2-byte aligned): lane roles rotated by the row's misalignment (1.58 vs 1.47 ms), and run-wise aligned
+                // words chosen per lane from the address's low bits with bytewise run ends (1.58 vs 1.34 ms).  This path is
+                // latency-bound, not issue-bound (issue slots 32 % busy): the shuffle + selector arithmetic lengthens the
+                // per-frame dependency chain more than the saved store instructions shorten it.
                 uint8_t* q = rb + (size_t)k * rstep * 3;
                 q[0] = (uint8_t)vB; q[1] = (uint8_t)vG; q[2] = (uint8_t)vR;
             }
@@ -883,13 +889,21 @@ template <int DTYPE, bool IDENT, bool WT>
 cudaError_t launch_rectify_t(const RectifyArgs& a, bool aligned4, int tiles_x, int out_align, int fast_ok, dim3 grid, cudaStream_t s)
 {
     if (a.batch_loop && !a.force_generic && a.src_pitch * (size_t)a.H < (1u << 31) && (size_t)a.W * a.H * 3 < (1u << 30)) {
-        const bool a4 = fast_ok && aligned4;
+        const bool a4 = fast_ok && aligned4 && !a.force_unaligned;
         const int tiles_y = (a.H + kTileH - 1) / kTileH;
-        // frames per CTA: enough CTAs for ~8 per SM slot (balance), as many frames per CTA as that allows (amortisation)
+        // frames per CTA.  Many short CTAs balance better (partial tiles at the image edge take longer than full ones, and
+        // the last wave of a launch is only as fast as its slowest CTA); long CTAs amortise the per-tile set-up.  Measured
+        // (profiles/r01_workloads.md): ~128 CTAs per SM as long as each still walks >= 12 frames.  batch_ctas > 0 fixes
+        // the CTAs per SM instead (tests use it to force one frame per CTA or the whole batch in one CTA).
         const long long tile_eyes = (long long)tiles_x * tiles_y * 2;
-        long long want = (long long)a.batch_loop * (a.batch_ctas_per_sm > 0 ? a.batch_ctas_per_sm : 8);   // a.batch_loop carries the SM count
+        const long long want = (long long)a.batch_loop * (a.batch_ctas_per_sm > 0 ? a.batch_ctas_per_sm : 128);   // a.batch_loop carries the SM count
         int fpc = (int)((tile_eyes * a.n + want - 1) / want);
         if (fpc < 1) fpc = 1;
+        if (a.batch_ctas_per_sm <= 0) {
+            if (fpc < 12) fpc = 12;
+            const int whole = a.n / fpc > 0 ? a.n / fpc : 1;            // chunks of at least fpc frames ...
+            fpc = (a.n + whole - 1) / whole;                            // ... of equal length
+        }
         if (fpc > a.n) fpc = a.n;
         const int chunks = (a.n + fpc - 1) / fpc;
         if (2 * chunks <= 65535) {

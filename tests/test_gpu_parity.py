@@ -81,7 +81,8 @@ def test_maps_absurd_calibrations(golden, calibs, tag):
 
 # ---- a3: rectified images -------------------------------------------------------------------------------------
 @pytest.mark.parametrize("name", ["calib_a", "calib_b", "calib_c_rational"])
-@pytest.mark.parametrize("variant", ["default", "tile_fastest", "force_direct", "force_generic", "persistent", "persistent_tile_fastest", "per_tile_cta", "no_bulk"])
+@pytest.mark.parametrize("variant", ["default", "tile_fastest", "force_direct", "force_generic", "persistent", "persistent_tile_fastest", "per_tile_cta", "no_bulk", "force_unaligned",
+                                     "no_l2_prefetch"])
 def test_rectified_demo_bit_exact(golden, demo_pair, name, variant):
     g_ = golden["cases"]["demo_" + name]
     l, r = demo_pair
@@ -97,6 +98,10 @@ def test_rectified_demo_bit_exact(golden, demo_pair, name, variant):
             g.set_option("batch_loop", 0)
         if variant == "no_bulk":
             g.set_option("bulk", 0)
+        if variant == "force_unaligned":
+            g.set_option("force_unaligned", 1)       # the W % 4 != 0 code path (funnel-shifted loads, run-wise word stores) on aligned frames
+        if variant == "no_l2_prefetch":
+            g.set_option("l2_prefetch", 0)
         if variant == "force_generic":
             g.set_option("force_generic", 1)
         g.load_calibration_yaml(os.path.join(GOLDEN, name + ".yml"))
@@ -433,6 +438,34 @@ def test_side_by_side_capture_frame(calibs, demo_pair):
                 li, ri = sbs[i, :, :640], sbs[i, :, 640:]
                 rl, rr = O.rectify_pair(c, np.ascontiguousarray(li), np.ascontiguousarray(ri))
                 assert np.array_equal(g.rectified(2, 0)[i], rl) and np.array_equal(g.rectified(2, 1)[i], rr)
+
+
+@pytest.mark.parametrize("size", [(1242, 375), (638, 50), (333, 77), (67, 19), (131, 33), (1241, 40)])
+@pytest.mark.parametrize("l2_prefetch", [2, 0])
+def test_rectified_unaligned_widths_batches(calibs, size, l2_prefetch):
+    """Widths that are not a multiple of 4: rows (and, for odd W*H, frames) start at every byte alignment, so the batch
+    kernel's funnel-shifted loads and its run-wise aligned-word stores (head/tail bytes at warp and row ends, partial tiles
+    at the right edge) see all four cases; several frames per CTA; tensors of the last frame checked too."""
+    W, H = size
+    s = W / 640
+    c = O.scale_calibration(calibs["calib_a"], s, crop_y=(480 * s - H) / 2)
+    n = 6
+    rng = np.random.default_rng(W * 1000 + H)
+    L = rng.integers(0, 256, (n, H, W, 3), dtype=np.uint8)
+    R = rng.integers(0, 256, (n, H, W, 3), dtype=np.uint8)
+    (l1, l2), (r1, r2) = O.rectify_maps(c, (W, H))
+    with geom(W, H, model="HitNet", max_batch=n) as g:
+        g.set_option("l2_prefetch", l2_prefetch)
+        g.set_option("batch_ctas", 1)                     # all frames in one CTA
+        g.set_calibration(c)
+        g.rectify_preprocess(L, R)
+        gl, gr = g.rectified(n, 0), g.rectified(n, 1)
+        for i in range(n):
+            assert np.array_equal(gl[i], OC.remap(L[i], l1, l2)), (size, i)
+            assert np.array_equal(gr[i], OC.remap(R[i], r1, r2)), (size, i)
+        t = g.tensor(n, 0)[n - 1]                         # HitNet: 6 planes, left RGB then right RGB
+        want = O.preprocess(O.HITNET, OC.remap(L[n - 1], l1, l2), OC.remap(R[n - 1], r1, r2), np.float32)
+        assert np.array_equal(t, want)
 
 
 @pytest.mark.parametrize("ctas_per_sm", [1, 16, 1000])
