@@ -138,6 +138,13 @@ SA_API float* sa_pointcloud_buffer(sa_handle* h);
  * (after RAFTStereo's sign flip).  out as for sa_reproject. */
 SA_API int sa_heatmap(sa_handle* h, int n, uint8_t* out, int where, sa_stream stream);
 
+/* The disparity as the 8-bit image the demos write: cv::imwrite("disparity.jpg", disparity) on a CV_32FC1 Mat
+ * (FastACVNet_plus/test/main.cpp:55, RAFTStereo/test/main.cpp:31) first does convertTo(CV_8U), i.e.
+ * saturate_cast<uchar>(cvRound(d)): round half to even, clamp to 0..255, NaN / +-inf / |d| >= 2^31 -> 0.
+ * out: uint8[n][h][w] (plane 0 of the disparity), device or host like sa_heatmap.  The JPEG encoding itself is not
+ * reproduced; sa_write_pgm (stereo_algorithms_compat.h) stores the bytes losslessly. */
+SA_API int sa_disparity_u8(sa_handle* h, int n, uint8_t* out, int where, sa_stream stream);
+
 /* Read-backs (the cudaMemcpy D2H + clone of TRTFastACVNet_plus.cpp:163-168; rectified images are what the
  * reference leaves in the caller's cv::Mat). */
 SA_API int sa_copy_rectified(sa_handle* h, int n, int eye, uint8_t* out, int where, sa_stream stream);
@@ -176,6 +183,19 @@ SA_API int sa_parse_calibration_yaml(const char* path, sa_calibration* out, char
  * (Q[3] = -cx', Q[7] = -cy', Q[11] = f', Q[15] *= scale; Q[14] = -1/Tx is unchanged).  in == out is allowed. */
 SA_API int sa_write_calibration_yaml(const char* path, const sa_calibration* c);
 SA_API int sa_scale_calibration(const sa_calibration* in, double scale, double crop_x, double crop_y, sa_calibration* out);
+/* Re-rectification: cv::stereoRectify as the reference's calibration tool calls it (Stereo_Calibration/Stereo_Calibration.cpp:162,
+ * flags = CALIB_ZERO_DISPARITY, alpha = 0, new size = image size), restated in f64 host code.  From the cameras (K, D with
+ * 0..14 coefficients), the image size and the pose R (3x3), T of the right camera it produces R_L, R_R (3x3), P1, P2 (3x4),
+ * Q (4x4, may be NULL) and the valid ROIs {x, y, w, h} (may be NULL) for an output of new_width x new_height (0 x 0 = image
+ * size).  alpha < 0: keep the focal length; 0: only valid pixels; 1: all source pixels.  sa_rectify_calibration applies it
+ * to a parsed calibration in place (uses K_*, D_*, R, T; overwrites R_L, R_R, P1, P2, Q).  Parity with OpenCV 4.13: see
+ * csrc/stereo_rectify.cpp. */
+#define SA_CALIB_ZERO_DISPARITY 1024 /* = cv::CALIB_ZERO_DISPARITY */
+SA_API int sa_stereo_rectify(const double* K_l, const double* D_l, int nD_l, const double* K_r, const double* D_r, int nD_r, int width, int height,
+                             const double* R, const double* T, int flags, double alpha, int new_width, int new_height, double* R_L, double* R_R,
+                             double* P1, double* P2, double* Q, int* roi_l, int* roi_r);
+SA_API int sa_rectify_calibration(sa_calibration* c, int width, int height, int flags, double alpha, int new_width, int new_height, int* roi_l,
+                                  int* roi_r);
 SA_API int sa_norm_lut(int model, float* lut768);
 SA_API int sa_resize_table(int dst, int src, int* table);
 

@@ -191,6 +191,46 @@ def main():
         assert np.array_equal(ref, mine), (tag, int((ref != mine).sum()))
         G["heatmap"][tag] = dict(shape=list(disp.shape), md5=md5(ref), disparity_md5=md5(disp))
 
+    # ---- disparity -> 8-bit image (what imwrite("disparity.jpg", CV_32FC1) encodes): cv2 PNG round trip ----------
+    G["disparity_u8"] = {}
+    special = np.array([[0.5, 1.5, 2.5, -3.2, 254.5, 255.5, 300, np.inf, -np.inf, np.nan, 0.49999997, 127.50001, 1e10, -1e10,
+                         2147483648.0, 3e9, 2147483520.0, -0.5, 255.49998, 63.5]], np.float32)
+    np.save(os.path.join(OUT, "disparity_u8_special.npy"), special)
+    for tag, disp in (("special", special),
+                      ("synthetic_640x480", O.synthetic_disparity(640, 480, 1234)),
+                      ("negated", -O.synthetic_disparity(320, 240, 5)),
+                      ("random", np.random.default_rng(9).normal(30, 80, (375, 1242)).astype(np.float32))):
+        import tempfile
+        with tempfile.TemporaryDirectory() as td:
+            cv2.imwrite(os.path.join(td, "d.png"), disp)                     # same convertTo(CV_8U) as the .jpg path, lossless container
+            ref = cv2.imread(os.path.join(td, "d.png"), cv2.IMREAD_UNCHANGED)
+        mine = O.disparity_u8(disp)
+        assert ref.dtype == np.uint8 and np.array_equal(ref.reshape(disp.shape), mine), (tag, int((ref.reshape(disp.shape) != mine).sum()))
+        G["disparity_u8"][tag] = dict(shape=list(disp.shape), md5=md5(ref), values=ref.reshape(-1).tolist() if tag == "special" else None)
+
+    # ---- stereoRectify (section 8f-2): cv2 outputs for 48 configurations ----------------------------------------
+    SR = []
+    worst = [0.0] * 5
+    roi_mismatch = 0
+    for name in ("calib_a", "calib_b", "calib_c_rational"):
+        c = O.load_calibration_yaml(os.path.join(OUT, name + ".yml"))
+        args = [c[k] for k in ("intrinsic_left", "distCoeffs_left", "intrinsic_right", "distCoeffs_right")]
+        for size, new_size in (((640, 480), (0, 0)), ((1920, 1080), (640, 480))):
+            for flags in (cv2.CALIB_ZERO_DISPARITY, 0):
+                for alpha in (-1.0, 0.0, 0.5, 1.0):
+                    ref = cv2.stereoRectify(*args, size, c["R"], c["T"], flags=flags, alpha=alpha, newImageSize=new_size)
+                    mine = O.stereo_rectify(*args, size, c["R"], c["T"], flags, alpha, new_size)
+                    for i in range(5):
+                        worst[i] = max(worst[i], float(np.abs(mine[i] - ref[i]).max() / max(1.0, np.abs(ref[i]).max())))
+                    roi_mismatch += tuple(mine[5]) != tuple(ref[5]) or tuple(mine[6]) != tuple(ref[6])
+                    SR.append(dict(calib=name, size=list(size), new_size=list(new_size), flags=int(flags), alpha=alpha,
+                                   R1=ref[0].ravel().tolist(), R2=ref[1].ravel().tolist(), P1=ref[2].ravel().tolist(), P2=ref[3].ravel().tolist(),
+                                   Q=ref[4].ravel().tolist(), roi1=[int(v) for v in ref[5]], roi2=[int(v) for v in ref[6]]))
+    assert max(worst) < 1e-12 and roi_mismatch <= 2, (worst, roi_mismatch)
+    print("stereoRectify: oracle vs cv2, worst scaled error per output", worst, "roi mismatches", roi_mismatch, "of", len(SR))
+    with open(os.path.join(OUT, "stereo_rectify.json"), "w") as f:
+        json.dump(dict(opencv=cv2.__version__, cases=SR), f)
+
     # ---- preprocess LUTs + reproject known answers (oracle-produced; the reference has no CPU
     #      code for these stages - they are pinned on the GPU box against the reference's own
     #      kernels compiled unmodified into oracle/_ref, see oracle/build_ref.py) ------------------

@@ -425,6 +425,186 @@ def heatmap(disparity: np.ndarray) -> np.ndarray:
 
 
 # ----------------------------------------------------------------------------------------------
+# f2. stereoRectify: Stereo_Calibration/Stereo_Calibration.cpp:162 calls
+#     stereoRectify(K_l, D_l, K_r, D_r, size, R, T, R_L, R_R, P1, P2, Q, CALIB_ZERO_DISPARITY, 0, size, &roiL, &roiR);
+#     OpenCV is not vendored in the reference: this restates cv::stereoRectify of OpenCV 4.13 (Bouguet) and is pinned
+#     against cv2.stereoRectify by oracle/gen_golden.py -> tests/golden/stereo_rectify.json.
+# ----------------------------------------------------------------------------------------------
+CALIB_ZERO_DISPARITY = 1024
+
+
+def rodrigues_to_matrix(r) -> np.ndarray:
+    r = np.asarray(r, np.float64).reshape(3)
+    theta = math.sqrt(float(r @ r))
+    if theta < np.finfo(np.float64).eps:
+        return np.eye(3)
+    c, s = math.cos(theta), math.sin(theta)
+    x, y, z = r / theta
+    rrt = np.array([[x * x, x * y, x * z], [x * y, y * y, y * z], [x * z, y * z, z * z]])
+    rx = np.array([[0, -z, y], [z, 0, -x], [-y, x, 0]])
+    return c * np.eye(3) + (1 - c) * rrt + s * rx
+
+
+def rodrigues_to_vector(R) -> np.ndarray:
+    """cv::Rodrigues matrix -> vector: nearest rotation (U Vt) first, then axis * angle (general case only)."""
+    u, _, vt = np.linalg.svd(np.asarray(R, np.float64).reshape(3, 3))
+    R = u @ vt
+    r = np.array([R[2, 1] - R[1, 2], R[0, 2] - R[2, 0], R[1, 0] - R[0, 1]])
+    s = math.sqrt(float(r @ r) * 0.25)
+    c = min(1.0, max(-1.0, (R[0, 0] + R[1, 1] + R[2, 2] - 1) * 0.5))
+    theta = math.acos(c)
+    if s < 1e-5:
+        if c > 0:
+            return np.zeros(3)
+        raise ValueError("rotation by pi: not needed for a stereo rig")
+    return r * (1.0 / (2 * s) * theta)
+
+
+def _undistort_point(u, v, K, k, RR=None):
+    """cv::undistortPoints for one point, default criteria = 5 iterations; k = 14 coefficients."""
+    fx, fy, cx, cy = K[0, 0], K[1, 1], K[0, 2], K[1, 2]
+    ifx, ify = 1.0 / fx, 1.0 / fy
+    x = (u - cx) * ifx
+    y = (v - cy) * ify
+    x0, y0 = x, y
+    for _ in range(5):
+        r2 = x * x + y * y
+        icdist = (1 + ((k[7] * r2 + k[6]) * r2 + k[5]) * r2) / (1 + ((k[4] * r2 + k[1]) * r2 + k[0]) * r2)
+        if icdist < 0:
+            x, y = (u - cx) * ifx, (v - cy) * ify
+            break
+        dx = 2 * k[2] * x * y + k[3] * (r2 + 2 * x * x) + k[8] * r2 + k[9] * r2 * r2
+        dy = k[2] * (r2 + 2 * y * y) + 2 * k[3] * x * y + k[10] * r2 + k[11] * r2 * r2
+        x = (x0 - dx) * icdist
+        y = (y0 - dy) * icdist
+    if RR is not None:
+        xx = RR[0, 0] * x + RR[0, 1] * y + RR[0, 2]
+        yy = RR[1, 0] * x + RR[1, 1] * y + RR[1, 2]
+        ww = 1.0 / (RR[2, 0] * x + RR[2, 1] * y + RR[2, 2])
+        x, y = xx * ww, yy * ww
+    return x, y
+
+
+def _mat3(a, b):
+    """3x3 product with OpenCV's summation order (no BLAS, no FMA)."""
+    return np.array([[sum(float(a[i, k]) * float(b[k, j]) for k in range(3)) for j in range(3)] for i in range(3)])
+
+
+def _undistort_rectangles(K, k, R, P, size):
+    N = 9
+    w, h = size
+    RR = _mat3(np.asarray(P, np.float64)[:3, :3], R)
+    FM = float(np.finfo(np.float32).max)
+    iX0, iX1, iY0, iY1 = -FM, FM, -FM, FM
+    oX0, oX1, oY0, oY1 = FM, -FM, FM, -FM
+    for y in range(N):
+        for x in range(N):
+            px, py = _undistort_point(float(x) * (w - 1) / (N - 1), float(y) * (h - 1) / (N - 1), K, k, RR)
+            oX0, oX1, oY0, oY1 = min(oX0, px), max(oX1, px), min(oY0, py), max(oY1, py)
+            if x == 0:
+                iX0 = max(iX0, px)
+            if x == N - 1:
+                iX1 = min(iX1, px)
+            if y == 0:
+                iY0 = max(iY0, py)
+            if y == N - 1:
+                iY1 = min(iY1, py)
+    return (iX0, iY0, iX1 - iX0, iY1 - iY0), (oX0, oY0, oX1 - oX0, oY1 - oY0)
+
+
+def stereo_rectify(K1, D1, K2, D2, size, R, T, flags=CALIB_ZERO_DISPARITY, alpha=-1.0, new_size=(0, 0)):
+    """-> R1, R2 (3x3), P1, P2 (3x4), Q (4x4), roi1, roi2 (x, y, w, h)."""
+    f32 = np.float32
+    K1, K2 = np.asarray(K1, np.float64).reshape(3, 3), np.asarray(K2, np.float64).reshape(3, 3)
+    ks = []
+    for D in (D1, D2):
+        k = np.zeros(14)
+        d = np.asarray(D, np.float64).ravel()
+        k[:len(d)] = d
+        ks.append(k)
+    nx, ny = size
+    T = np.asarray(T, np.float64).reshape(3)
+    r_r = rodrigues_to_matrix(rodrigues_to_vector(R) * -0.5)          # each camera turns half way
+    t = np.array([sum(float(r_r[i, j]) * float(T[j]) for j in range(3)) for i in range(3)])
+    idx = 0 if abs(t[0]) > abs(t[1]) else 1
+    c, nt = t[idx], math.sqrt(float(t[0] * t[0] + t[1] * t[1] + t[2] * t[2]))
+    uu = np.zeros(3)
+    uu[idx] = 1 if c > 0 else -1
+    ww = np.array([t[1] * uu[2] - t[2] * uu[1], t[2] * uu[0] - t[0] * uu[2], t[0] * uu[1] - t[1] * uu[0]])
+    nw = math.sqrt(float(ww[0] * ww[0] + ww[1] * ww[1] + ww[2] * ww[2]))
+    if nw > 0:
+        ww = ww * (math.acos(abs(c) / nt) / nw)
+    wR = rodrigues_to_matrix(ww)
+    R1, R2 = _mat3(wR, r_r.T), _mat3(wR, r_r)
+    t = np.array([sum(float(R2[i, j]) * float(T[j]) for j in range(3)) for i in range(3)])
+    W, H = new_size if new_size[0] * new_size[1] != 0 else size
+    ratio = (W / nx / 2) if idx == 1 else (H / ny / 2)
+    fc = (K1[idx ^ 1, idx ^ 1] + K2[idx ^ 1, idx ^ 1]) * ratio
+    cc = []
+    for K, k, Rk in ((K1, ks[0], R1), (K2, ks[1], R2)):
+        ax = ay = 0.0
+        for i in range(4):                                            # image corners; OpenCV keeps them as float
+            x, y = _undistort_point(float(f32((i % 2) * (nx - 1))), float(f32((0 if i < 2 else 1) * (ny - 1))), K, k)
+            X = (float(f32(x)), float(f32(y)), 1.0)
+            Y = [Rk[j, 0] * X[0] + Rk[j, 1] * X[1] + Rk[j, 2] * X[2] for j in range(3)]
+            z = 1.0 / Y[2] if Y[2] != 0 else 1.0
+            ax += float(f32(fc * (Y[0] * z)))
+            ay += float(f32(fc * (Y[1] * z)))
+        cc.append([(nx - 1) / 2 - ax / 4, (ny - 1) / 2 - ay / 4])
+    if flags & CALIB_ZERO_DISPARITY:
+        cc[0][0] = cc[1][0] = (cc[0][0] + cc[1][0]) * 0.5
+        cc[0][1] = cc[1][1] = (cc[0][1] + cc[1][1]) * 0.5
+    elif idx == 0:
+        cc[0][1] = cc[1][1] = (cc[0][1] + cc[1][1]) * 0.5
+    else:
+        cc[0][0] = cc[1][0] = (cc[0][0] + cc[1][0]) * 0.5
+    P1 = np.zeros((3, 4))
+    P1[0, 0] = P1[1, 1] = fc
+    P1[0, 2], P1[1, 2], P1[2, 2] = cc[0][0], cc[0][1], 1
+    P2 = P1.copy()
+    P2[0, 2], P2[1, 2] = cc[1][0], cc[1][1]
+    P2[idx, 3] = t[idx] * fc
+    alpha = min(alpha, 1.0)
+    in1, out1 = _undistort_rectangles(K1, ks[0], R1, P1, size)
+    in2, out2 = _undistort_rectangles(K2, ks[1], R2, P2, size)
+    (cx1_0, cy1_0), (cx2_0, cy2_0) = cc
+    cx1, cy1, cx2, cy2 = W * cx1_0 / nx, H * cy1_0 / ny, W * cx2_0 / nx, H * cy2_0 / ny
+    s = 1.0
+    if alpha >= 0:
+        def ext(cx, cy, cx0, cy0, r, fn):
+            x, y, w, h = r
+            return fn(fn(fn(cx / (cx0 - x), cy / (cy0 - y)), (W - 1 - cx) / (x + w - cx0)), (H - 1 - cy) / (y + h - cy0))
+        s0 = max(ext(cx2, cy2, cx2_0, cy2_0, in2, max), ext(cx1, cy1, cx1_0, cy1_0, in1, max))
+        s1 = min(ext(cx2, cy2, cx2_0, cy2_0, out2, min), ext(cx1, cy1, cx1_0, cy1_0, out1, min))
+        s = s0 * (1 - alpha) + s1 * alpha
+    fc *= s
+    P1[0, 0] = P1[1, 1] = P2[0, 0] = P2[1, 1] = fc
+    P1[0, 2], P1[1, 2], P2[0, 2], P2[1, 2] = cx1, cy1, cx2, cy2
+    P2[idx, 3] = s * P2[idx, 3]
+
+    def roi(inn, cx0, cy0, cx, cy):
+        x, y, w, h = inn
+        rx, ry = math.ceil((x - cx0) * s + cx), math.ceil((y - cy0) * s + cy)
+        rw, rh = math.floor(w * s), math.floor(h * s)
+        x0, y0, x1, y1 = max(rx, 0), max(ry, 0), min(rx + rw, W), min(ry + rh, H)
+        return (0, 0, 0, 0) if x1 <= x0 or y1 <= y0 else (x0, y0, x1 - x0, y1 - y0)
+    Q = np.array([[1, 0, 0, -cx1], [0, 1, 0, -cy1], [0, 0, 0, fc], [0, 0, -1.0 / t[idx], ((cx1 - cx2) if idx == 0 else (cy1 - cy2)) / t[idx]]])
+    return R1, R2, P1, P2, Q, roi(in1, cx1_0, cy1_0, cx1, cy1), roi(in2, cx2_0, cy2_0, cx2, cy2)
+
+
+
+def disparity_u8(disparity: np.ndarray) -> np.ndarray:
+    """What cv::imwrite("disparity.jpg", disparity) encodes (FastACVNet_plus/test/main.cpp:55): imwrite converts a
+    CV_32FC1 Mat with convertTo(CV_8U) = saturate_cast<uchar>(cvRound(d)); cvRound (cvtss2si) rounds half to even and
+    returns INT_MIN for NaN and |d| >= 2^31, which saturates to 0.  Pinned against cv2 (PNG round trip) in gen_golden.py."""
+    d = np.asarray(disparity, np.float32)
+    with np.errstate(all="ignore"):
+        r = np.rint(d.astype(np.float64))
+        ok = np.abs(d) < np.float32(2147483648.0)          # False for NaN
+    return np.where(ok, np.clip(np.where(ok, r, 0.0), 0, 255), 0).astype(np.uint8)
+
+
+# ----------------------------------------------------------------------------------------------
 # synthetic inputs (SURVEY.md section 8d) - deterministic, shared by tests and bench baselines
 # ----------------------------------------------------------------------------------------------
 def synthetic_disparity(W: int, H: int, seed: int = 1234, invalid: bool = True) -> np.ndarray:

@@ -60,6 +60,7 @@ SIGNATURES = {
     "sa_reproject": (_i, [_vp, _i, _i, _vp, _vp, _i, _vp]),
     "sa_pointcloud_buffer": (_vp, [_vp]),
     "sa_heatmap": (_i, [_vp, _i, _vp, _i, _vp]),
+    "sa_disparity_u8": (_i, [_vp, _i, _vp, _i, _vp]),
     "sa_copy_rectified": (_i, [_vp, _i, _i, _vp, _i, _vp]),
     "sa_copy_net_image": (_i, [_vp, _i, _i, _vp, _i, _vp]),
     "sa_copy_tensor": (_i, [_vp, _i, _i, _vp, _i, _vp]),
@@ -69,6 +70,8 @@ SIGNATURES = {
     "sa_run_batch": (_i, [_vp, _i, _vp, _vp, _i, _u, _vp, _vp, _vp, _vp, _vp]),
     "sa_parse_calibration_yaml": (_i, [_cp, C.POINTER(sa_calibration), C.c_char_p, _sz]),
     "sa_write_calibration_yaml": (_i, [_cp, C.POINTER(sa_calibration)]),
+    "sa_stereo_rectify": (_i, [_vp, _vp, _i, _vp, _vp, _i, _i, _i, _vp, _vp, _i, C.c_double, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "sa_rectify_calibration": (_i, [C.POINTER(sa_calibration), _i, _i, _i, C.c_double, _i, _i, _vp, _vp]),
     "sa_scale_calibration": (_i, [C.POINTER(sa_calibration), C.c_double, C.c_double, C.c_double, C.POINTER(sa_calibration)]),
     "sa_norm_lut": (_i, [_i, _vp]),
     "sa_resize_table": (_i, [_i, _i, _vp]),
@@ -91,6 +94,8 @@ SIGNATURES = {
     "sa_ref_Heatmap": (_i, [_vp, _vp]),
     "sa_write_pointcloud_txt": (_i, [_cp, _vp, _sz]),
     "sa_write_pointcloud_ply": (_i, [_cp, _vp, _sz, _i, _i]),
+    "sa_write_pgm": (_i, [_cp, _vp, _i, _i, _sz]),
+    "sa_write_ppm_bgr": (_i, [_cp, _vp, _i, _i, _sz]),
 }
 
 _lib = None

@@ -127,3 +127,19 @@ def write_pointcloud_ply(path: str, pointcloud: np.ndarray, binary: bool = True,
     rc = L.load().sa_write_pointcloud_ply(path.encode(), pts.ctypes.data, pts.shape[0], 1 if binary else 0, 1 if skip_non_finite else 0)
     if rc != 0:
         raise OSError(f"sa_write_pointcloud_ply({path}) failed with {rc}")
+
+
+def write_pgm(path: str, grey: np.ndarray) -> None:
+    """8-bit grey image as binary PGM - lossless stand-in for cv::imwrite("disparity.jpg", ...) of the demos."""
+    g = np.ascontiguousarray(grey, np.uint8)
+    rc = L.load().sa_write_pgm(path.encode(), g.ctypes.data, g.shape[1], g.shape[0], 0)
+    if rc != 0:
+        raise OSError(f"sa_write_pgm({path}) failed with {rc}")
+
+
+def write_ppm(path: str, bgr: np.ndarray) -> None:
+    """BGR uint8 HxWx3 image (rectified frame, heat map) as binary PPM (stored RGB)."""
+    b = np.ascontiguousarray(bgr, np.uint8)
+    rc = L.load().sa_write_ppm_bgr(path.encode(), b.ctypes.data, b.shape[1], b.shape[0], 0)
+    if rc != 0:
+        raise OSError(f"sa_write_ppm_bgr({path}) failed with {rc}")

@@ -715,6 +715,21 @@ int sa_heatmap(sa_handle* h, int n, uint8_t* out, int where, sa_stream stream)
     return SA_OK;
 }
 
+int sa_disparity_u8(sa_handle* h, int n, uint8_t* out, int where, sa_stream stream)
+{
+    SA_ENTER(h);
+    SA_CHECK_N(h, n);
+    if (!out) return fail(h, SA_ERR_INVALID_ARG, "sa_disparity_u8: null");
+    if (n == 0) return SA_OK;
+    cudaStream_t s = pick(h, stream);
+    uint8_t* dev = where == SA_DEVICE ? out : h->heat;               // host output: staged in the heatmap buffer (3x as large)
+    if (!dev) return fail(h, SA_ERR_INVALID_ARG, "sa_disparity_u8: no internal staging buffer (SA_FLAG_NO_HEATMAP_BUF); pass a device `out`");
+    const size_t npix = (size_t)h->w * h->h;
+    SA_CUDA(h, launch_disparity_u8(h->disp, disp_frame_floats(h), npix, n, dev, s, &h->launches));
+    if (where == SA_HOST) return copy_out(h, out, dev, (size_t)n * npix, SA_HOST, s);
+    return SA_OK;
+}
+
 int sa_copy_rectified(sa_handle* h, int n, int eye, uint8_t* out, int where, sa_stream stream)
 {
     SA_ENTER(h);

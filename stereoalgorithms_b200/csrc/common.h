@@ -215,6 +215,7 @@ cudaError_t launch_minmax(const float* disp, size_t disp_frame, int npix, int n,
 cudaError_t launch_heatmap(const float* disp, size_t disp_frame, int npix, int n, const unsigned* minmax, uint8_t* out, cudaStream_t s, long* launches);
 cudaError_t launch_stub(float* disp, size_t disp_frame, int planes, int w, int h, int first_frame, int n, unsigned seed, int negate,
                         cudaStream_t s, long* launches);
+cudaError_t launch_disparity_u8(const float* disp, size_t disp_frame, size_t npix, int n, uint8_t* out, cudaStream_t s, long* launches);
 cudaError_t launch_copy_plane0(const float* disp, size_t disp_frame, size_t npix, int n, float* out, cudaStream_t s, long* launches);
 
 void build_norm_lut(int model, float* lut /*[3][256]*/);

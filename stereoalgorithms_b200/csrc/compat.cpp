@@ -227,4 +227,33 @@ int sa_write_pointcloud_ply(const char* path, const float* points, size_t n_poin
     return std::fclose(f) == 0 ? SA_OK : SA_ERR_IO;
 }
 
+int sa_write_pgm(const char* path, const uint8_t* grey, int w, int h, size_t step)
+{
+    if (!path || !grey || w <= 0 || h <= 0 || (step != 0 && step < (size_t)w)) return SA_ERR_INVALID_ARG;
+    FILE* f = std::fopen(path, "wb");
+    if (!f) return SA_ERR_IO;
+    std::fprintf(f, "P5\n%d %d\n255\n", w, h);
+    const size_t st = step ? step : (size_t)w;
+    bool ok = true;
+    for (int y = 0; y < h && ok; y++) ok = std::fwrite(grey + (size_t)y * st, 1, (size_t)w, f) == (size_t)w;
+    return (std::fclose(f) == 0 && ok) ? SA_OK : SA_ERR_IO;
+}
+
+int sa_write_ppm_bgr(const char* path, const uint8_t* bgr, int w, int h, size_t step)
+{
+    if (!path || !bgr || w <= 0 || h <= 0 || (step != 0 && step < (size_t)w * 3)) return SA_ERR_INVALID_ARG;
+    FILE* f = std::fopen(path, "wb");
+    if (!f) return SA_ERR_IO;
+    std::fprintf(f, "P6\n%d %d\n255\n", w, h);
+    const size_t st = step ? step : (size_t)w * 3;
+    std::vector<uint8_t> row((size_t)w * 3);
+    bool ok = true;
+    for (int y = 0; y < h && ok; y++) {
+        const uint8_t* p = bgr + (size_t)y * st;
+        for (int x = 0; x < w; x++) { row[3 * x] = p[3 * x + 2]; row[3 * x + 1] = p[3 * x + 1]; row[3 * x + 2] = p[3 * x]; }
+        ok = std::fwrite(row.data(), 1, row.size(), f) == row.size();
+    }
+    return (std::fclose(f) == 0 && ok) ? SA_OK : SA_ERR_IO;
+}
+
 }  // extern "C"

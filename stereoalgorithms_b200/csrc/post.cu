@@ -132,6 +132,33 @@ __global__ void __launch_bounds__(256) copy_plane0_kernel(const float* __restric
     if (p < npix) out[(size_t)frame * npix + p] = disp[(size_t)frame * disp_frame + p];
 }
 
+// ---- disparity as an 8-bit image: what cv::imwrite("disparity.jpg", disparity) encodes (FastACVNet_plus/test/main.cpp:55) ----
+// imwrite converts a CV_32FC1 Mat with convertTo(CV_8U): saturate_cast<uchar>(cvRound(d)).  cvRound is cvtss2si: round half
+// to even, and 0x80000000 for NaN and for |d| >= 2^31 - which saturates to 0, not 255 (probed with cv2 4.13: +inf -> 0).
+__device__ __forceinline__ uint32_t disparity_to_u8(float d)
+{
+    if (!(fabsf(d) < 2147483648.0f)) return 0u;
+    return (uint32_t)min(255, max(0, __float2int_rn(d)));
+}
+
+template <bool VEC>
+__global__ void __launch_bounds__(256) disparity_u8_kernel(const float* __restrict__ disp, size_t disp_frame, size_t npix, uint8_t* __restrict__ out)
+{
+    const int frame = blockIdx.y;
+    const float* d = disp + (size_t)frame * disp_frame;
+    uint8_t* o = out + (size_t)frame * npix;
+    const size_t p = ((size_t)blockIdx.x * 256 + threadIdx.x) * 4;
+    if (VEC) {
+        if (p < npix) {
+            const float4 t = *reinterpret_cast<const float4*>(d + p);
+            *reinterpret_cast<uint32_t*>(o + p) = disparity_to_u8(t.x) | (disparity_to_u8(t.y) << 8) | (disparity_to_u8(t.z) << 16) | (disparity_to_u8(t.w) << 24);
+        }
+    } else {
+        for (int k = 0; k < 4; k++)
+            if (p + k < npix) o[p + k] = (uint8_t)disparity_to_u8(d[p + k]);
+    }
+}
+
 // ---- u8 resize (extension a8): OpenCV's fixed-point INTER_LINEAR for downscales ----------------------------
 __global__ void __launch_bounds__(256) resize_kernel(const ResizeArgs a)
 {
@@ -199,6 +226,17 @@ cudaError_t launch_copy_plane0(const float* disp, size_t disp_frame, size_t npix
 {
     if (n <= 0) return cudaSuccess;
     copy_plane0_kernel<<<dim3((unsigned)((npix + 255) / 256), (unsigned)n), 256, 0, s>>>(disp, disp_frame, npix, out);
+    if (launches) ++*launches;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_disparity_u8(const float* disp, size_t disp_frame, size_t npix, int n, uint8_t* out, cudaStream_t s, long* launches)
+{
+    if (n <= 0) return cudaSuccess;
+    const bool vec = npix % 4 == 0 && disp_frame % 4 == 0 && ((uintptr_t)disp) % 16 == 0 && ((uintptr_t)out) % 4 == 0;
+    const dim3 grid((unsigned)((npix + 1023) / 1024), (unsigned)n);
+    if (vec) disparity_u8_kernel<true><<<grid, 256, 0, s>>>(disp, disp_frame, npix, out);
+    else disparity_u8_kernel<false><<<grid, 256, 0, s>>>(disp, disp_frame, npix, out);
     if (launches) ++*launches;
     return cudaGetLastError();
 }

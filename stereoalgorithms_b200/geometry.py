@@ -190,6 +190,17 @@ class StereoGeometry:
         self._check(self._lib.sa_heatmap(self._h, n, po, DEVICE, stream))
         return out
 
+    def disparity_u8(self, n: int, out=None, to_host: bool = True, stream=None):
+        """The disparity as cv::imwrite("disparity.jpg", disparity) sees it (FastACVNet_plus/test/main.cpp:55):
+        convertTo(CV_8U) of the float image -> uint8 [n, h, w]."""
+        if to_host:
+            img = np.empty((n, self.h, self.w), np.uint8) if out is None else out
+            self._check(self._lib.sa_disparity_u8(self._h, n, img.ctypes.data, HOST, stream))
+            return img
+        po, _ = _ptr(out)
+        self._check(self._lib.sa_disparity_u8(self._h, n, po, DEVICE, stream))
+        return out
+
     # -- read-backs ---------------------------------------------------------------------------------------------
     def rectified(self, n: int, eye: int) -> np.ndarray:
         out = np.empty((n, self.H, self.W, 3), np.uint8)
@@ -271,3 +282,22 @@ class PinnedArray:
             self._addr = None
 
     __del__ = free
+
+
+def stereo_rectify(K_l, D_l, K_r, D_r, size, R, T, flags: int = 1024, alpha: float = 0.0, new_size=(0, 0)):
+    """cv::stereoRectify as the reference's calibration tool calls it (Stereo_Calibration/Stereo_Calibration.cpp:162:
+    CALIB_ZERO_DISPARITY = 1024, alpha 0, new size = image size) -> R_L, R_R (3x3), P1, P2 (3x4), Q (4x4), roi_l, roi_r
+    (x, y, w, h).  Host code (sa_stereo_rectify); needs no GPU."""
+    lib = L.load()
+    a = lambda x: np.ascontiguousarray(np.asarray(x, np.float64).ravel())
+    K_l, D_l, K_r, D_r, R, T = (a(v) for v in (K_l, D_l, K_r, D_r, R, T))
+    if K_l.size != 9 or K_r.size != 9 or R.size != 9 or T.size != 3:
+        raise ValueError("K_l, K_r, R must have 9 elements and T 3")
+    R1, R2, P1, P2, Q = np.zeros((3, 3)), np.zeros((3, 3)), np.zeros((3, 4)), np.zeros((3, 4)), np.zeros((4, 4))
+    r1, r2 = np.zeros(4, np.int32), np.zeros(4, np.int32)
+    rc = lib.sa_stereo_rectify(K_l.ctypes.data, D_l.ctypes.data, D_l.size, K_r.ctypes.data, D_r.ctypes.data, D_r.size, int(size[0]), int(size[1]),
+                               R.ctypes.data, T.ctypes.data, int(flags), float(alpha), int(new_size[0]), int(new_size[1]), R1.ctypes.data, R2.ctypes.data,
+                               P1.ctypes.data, P2.ctypes.data, Q.ctypes.data, r1.ctypes.data, r2.ctypes.data)
+    if rc != 0:
+        raise StereoGeomError(rc, "sa_stereo_rectify: invalid argument")
+    return R1, R2, P1, P2, Q, tuple(int(v) for v in r1), tuple(int(v) for v in r2)

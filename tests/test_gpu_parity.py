@@ -296,6 +296,28 @@ def test_heatmap_golden(golden):
             assert md5(hm[0]) == golden["heatmap"][tag]["md5"], tag
 
 
+def test_disparity_u8_golden(golden):
+    """sa_disparity_u8 = the convertTo(CV_8U) inside cv::imwrite("disparity.jpg", disparity): vectors made by cv2."""
+    import torch
+    cases = {"special": np.load(os.path.join(GOLDEN, "disparity_u8_special.npy")),
+             "synthetic_640x480": O.synthetic_disparity(640, 480, 1234),
+             "negated": -O.synthetic_disparity(320, 240, 5),
+             "random": np.random.default_rng(9).normal(30, 80, (375, 1242)).astype(np.float32)}
+    for tag, d in cases.items():
+        H, W = d.shape
+        with geom(W, H, model="CREStereo", max_batch=2) as g:          # two planes per frame: plane 0 is the disparity
+            x = np.full((2, 2, H, W), 777.0, np.float32)                # plane 1 must be ignored
+            x[0, 0], x[1, 0] = d, d[::-1]
+            g.set_disparity(x)
+            img = g.disparity_u8(2)
+            assert md5(img[0]) == golden["disparity_u8"][tag]["md5"], tag
+            assert np.array_equal(img[1], O.disparity_u8(d[::-1])), tag
+            dev = torch.empty((2, H, W), dtype=torch.uint8, device="cuda")
+            g.disparity_u8(2, out=dev, to_host=False)
+            g.synchronize()
+            assert np.array_equal(dev.cpu().numpy(), img), tag
+
+
 def test_heatmap_after_reproject_uses_fused_minmax(calibs, demo_pair):
     from stereoalgorithms_b200.geometry import DENSE
     d = np.stack([O.synthetic_disparity(640, 480, 40 + i) * (1 + i) for i in range(3)])

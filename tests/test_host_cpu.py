@@ -169,6 +169,69 @@ def test_pointcloud_ply_writer(lib, tmp_path):
     assert len(lines) == 4 and lines[0] == "1.5 -0.25 2 255 0 12" and lines[3] == "3 4 5 7 8 9"
 
 
+def _lib_stereo_rectify(lib, c, size, new_size, flags, alpha):
+    a = lambda x: np.ascontiguousarray(np.asarray(x, np.float64).ravel())
+    K1, D1, K2, D2, R, T = (a(c[k]) for k in ("intrinsic_left", "distCoeffs_left", "intrinsic_right", "distCoeffs_right", "R", "T"))
+    R1, R2, P1, P2, Q = np.zeros(9), np.zeros(9), np.zeros(12), np.zeros(12), np.zeros(16)
+    r1, r2 = np.zeros(4, np.int32), np.zeros(4, np.int32)
+    rc = lib.sa_stereo_rectify(K1.ctypes.data, D1.ctypes.data, len(D1), K2.ctypes.data, D2.ctypes.data, len(D2), size[0], size[1], R.ctypes.data,
+                               T.ctypes.data, flags, alpha, new_size[0], new_size[1], R1.ctypes.data, R2.ctypes.data, P1.ctypes.data, P2.ctypes.data,
+                               Q.ctypes.data, r1.ctypes.data, r2.ctypes.data)
+    assert rc == 0
+    return R1, R2, P1, P2, Q, r1, r2
+
+
+def test_stereo_rectify_matches_opencv_golden(lib):
+    """sa_stereo_rectify (csrc/stereo_rectify.cpp) against cv2.stereoRectify 4.13 on the 48 golden configurations,
+    same gates as the oracle's own test."""
+    from test_oracle_golden import _check_stereo_rectify
+    assert _check_stereo_rectify(lambda c, size, new_size, flags, alpha: _lib_stereo_rectify(lib, c, size, new_size, flags, alpha)) == 48
+
+
+def test_rectify_calibration_in_place_and_maps_follow(lib, tmp_path):
+    """The tool's flow (Stereo_Calibration.cpp:162-179): rectify the parsed cameras for a new size, write the file, read it
+    back; and bad arguments are refused."""
+    from stereoalgorithms_b200._lib import sa_calibration
+    rc, c, err = _parse(lib, os.path.join(GOLDEN, "calib_a.yml"))
+    assert rc == 0, err
+    roi_l, roi_r = np.zeros(4, np.int32), np.zeros(4, np.int32)
+    assert lib.sa_rectify_calibration(C.byref(c), 640, 480, 1024, 0.0, 1280, 960, roi_l.ctypes.data, roi_r.ctypes.data) == 0
+    want = O.load_calibration_yaml(os.path.join(GOLDEN, "calib_a.yml"))
+    R1, R2, P1, P2, Q, w1, w2 = O.stereo_rectify(want["intrinsic_left"], want["distCoeffs_left"], want["intrinsic_right"], want["distCoeffs_right"],
+                                                 (640, 480), want["R"], want["T"], 1024, 0.0, (1280, 960))
+    assert np.allclose(np.array(c.P1), P1.ravel(), rtol=1e-11, atol=0) and np.allclose(np.array(c.Q), Q.ravel(), rtol=1e-11, atol=1e-15)
+    assert np.allclose(np.array(c.R_L), R1.ravel(), rtol=0, atol=1e-12) and np.allclose(np.array(c.R_R), R2.ravel(), rtol=0, atol=1e-12)
+    assert max(abs(int(a) - int(b)) for a, b in zip(list(roi_l) + list(roi_r), list(w1) + list(w2))) <= 1
+    assert c.P1[0] > 2 * 400 and abs(c.P2[3] / c.P2[0] + 1.0 / c.Q[14]) < 1e-9                 # twice the size: focal ~2x; P2[0,3] = f * Tx, Q[3,2] = -1/Tx
+    out = str(tmp_path / "rerectified.yml")
+    assert lib.sa_write_calibration_yaml(out.encode(), C.byref(c)) == 0
+    back = O.load_calibration_yaml(out)
+    assert np.array_equal(back["P2"].ravel(), np.array(c.P2)) and np.array_equal(back["R_R"].ravel(), np.array(c.R_R))
+    assert lib.sa_rectify_calibration(None, 640, 480, 0, 0.0, 0, 0, None, None) < 0
+    assert lib.sa_rectify_calibration(C.byref(c), 0, 480, 0, 0.0, 0, 0, None, None) < 0
+
+
+def test_netpbm_writers(lib, tmp_path):
+    """Lossless stand-ins for the demos' imwrite("disparity.jpg") / imwrite("heatmap.jpg") (FastACVNet_plus/test/main.cpp:55,59)."""
+    rng = np.random.default_rng(0)
+    grey = rng.integers(0, 256, (7, 13), dtype=np.uint8)
+    p = str(tmp_path / "d.pgm")
+    assert lib.sa_write_pgm(p.encode(), grey.ctypes.data, 13, 7, 0) == 0
+    raw = open(p, "rb").read()
+    assert raw.startswith(b"P5\n13 7\n255\n") and raw[len(b"P5\n13 7\n255\n"):] == grey.tobytes()
+    bgr = rng.integers(0, 256, (5, 9, 3), dtype=np.uint8)
+    padded = np.zeros((5, 40), np.uint8)
+    padded[:, :27] = bgr.reshape(5, 27)
+    q = str(tmp_path / "h.ppm")
+    assert lib.sa_write_ppm_bgr(q.encode(), padded.ctypes.data, 9, 5, 40) == 0       # pitched rows
+    raw = open(q, "rb").read()
+    assert raw.startswith(b"P6\n9 5\n255\n") and raw[len(b"P6\n9 5\n255\n"):] == bgr[..., ::-1].tobytes()
+    cv2 = pytest.importorskip("cv2")                                                  # OpenCV reads both back
+    assert np.array_equal(cv2.imread(p, cv2.IMREAD_UNCHANGED), grey) and np.array_equal(cv2.imread(q), bgr)
+    assert lib.sa_write_pgm(p.encode(), None, 13, 7, 0) < 0 and lib.sa_write_ppm_bgr(q.encode(), bgr.ctypes.data, 9, 5, 8) < 0
+    assert lib.sa_write_pgm(str(tmp_path / "no" / "dir.pgm").encode(), grey.ctypes.data, 13, 7, 0) < 0
+
+
 @pytest.mark.parametrize("name", ["calib_a", "calib_c_rational"])
 def test_calibration_writer_round_trip_and_scaling(lib, name, tmp_path):
     from stereoalgorithms_b200._lib import sa_calibration

@@ -104,6 +104,64 @@ def test_heatmap_golden(golden):
         assert md5(OC.heatmap(disp, O.jet_lut_bgr())) == g["md5"], tag
 
 
+def _check_stereo_rectify(fn):
+    """fn(calib dict, size, new_size, flags, alpha) -> R1, R2, P1, P2, Q, roi1, roi2; compared with cv2.stereoRectify 4.13
+    (tests/golden/stereo_rectify.json).  Gates: rotations 1e-12 absolute, P/Q 1e-11 relative to the matrix's largest
+    entry, ROIs equal - except at most 2 of the 48 cases by one pixel: with alpha = 0 an inner edge lands on the image
+    border by construction and the ROI is a ceil()/floor() of +-1e-13."""
+    import json
+    G = json.load(open(os.path.join(GOLDEN, "stereo_rectify.json")))
+    calibs = {}
+    off_by_one = 0
+    for g in G["cases"]:
+        c = calibs.setdefault(g["calib"], O.load_calibration_yaml(os.path.join(GOLDEN, g["calib"] + ".yml")))
+        got = fn(c, tuple(g["size"]), tuple(g["new_size"]), g["flags"], g["alpha"])
+        for i, key in enumerate(("R1", "R2", "P1", "P2", "Q")):
+            ref = np.array(g[key])
+            d = np.abs(np.asarray(got[i], np.float64).ravel() - ref).max()
+            tol = 1e-12 if key[0] == "R" else 1e-11 * np.abs(ref).max()
+            assert d <= tol, (g["calib"], g["size"], g["new_size"], g["flags"], g["alpha"], key, d)
+        for key, r in (("roi1", got[5]), ("roi2", got[6])):
+            r = [int(v) for v in r]
+            if r != g[key]:
+                assert max(abs(a - b) for a, b in zip(r, g[key])) <= 1, (g, key, r)
+                off_by_one += 1
+    assert off_by_one <= 2, off_by_one
+    return len(G["cases"])
+
+
+def test_stereo_rectify_golden():
+    n = _check_stereo_rectify(lambda c, size, new_size, flags, alpha: O.stereo_rectify(
+        c["intrinsic_left"], c["distCoeffs_left"], c["intrinsic_right"], c["distCoeffs_right"], size, c["R"], c["T"], flags, alpha, new_size))
+    assert n == 48
+
+
+def test_stereo_rectify_reproduces_the_fixture_rotations():
+    """The reference's own calibration files were written by stereoRectify (Stereo_Calibration.cpp:162-176): re-deriving
+    R_L / R_R from their R, T gives the stored matrices to the digits another OpenCV version agrees on."""
+    for name in ("calib_a", "calib_b", "calib_c_rational"):
+        c = O.load_calibration_yaml(os.path.join(GOLDEN, name + ".yml"))
+        R1, R2 = O.stereo_rectify(c["intrinsic_left"], c["distCoeffs_left"], c["intrinsic_right"], c["distCoeffs_right"], (640, 480), c["R"], c["T"])[:2]
+        assert np.abs(R1 - c["R_L"]).max() < 5e-6 and np.abs(R2 - c["R_R"]).max() < 5e-6, name
+
+
+def _disp_u8_inputs():
+    return {"special": np.load(os.path.join(GOLDEN, "disparity_u8_special.npy")),
+            "synthetic_640x480": O.synthetic_disparity(640, 480, 1234),
+            "negated": -O.synthetic_disparity(320, 240, 5),
+            "random": np.random.default_rng(9).normal(30, 80, (375, 1242)).astype(np.float32)}
+
+
+def test_disparity_u8_golden(golden):
+    """imwrite("disparity.jpg", CV_32FC1) = convertTo(CV_8U): vectors produced by cv2 (oracle/gen_golden.py)."""
+    for tag, disp in _disp_u8_inputs().items():
+        g = golden["disparity_u8"][tag]
+        got = O.disparity_u8(disp)
+        assert md5(got) == g["md5"], tag
+        if g["values"] is not None:
+            assert got.reshape(-1).tolist() == g["values"]      # +-inf, NaN, 1e10, 2^31 -> 0; 2.5 -> 2; 255.5 -> 255
+
+
 def test_norm_lut(golden):
     for m, n in O.MODEL_NAMES.items():
         assert md5(O.norm_lut(m)) == golden["norm_lut_md5"][n]
