@@ -104,6 +104,7 @@ struct sa_handle {
     long opt_persistent = 0;          // CTAs per SM of the persistent rectify kernel (0 = one CTA per tile, the default: measured faster)
     long opt_batch_ctas = 0;           // CTAs per SM of the batch kernel; 0 = automatic (launch_rectify_t)
     long opt_force_unaligned = 0;
+    long opt_no_fixed_size = 0;
     long opt_l2_prefetch = -1;        // see RectifyArgs::l2_prefetch; -1 = automatic
     long opt_bulk = 0;                // rectify_tma_kernel when the frames are 16-byte aligned
     long opt_batch_loop = 1;          // rectify_batch_kernel (default); 0 = one CTA per (tile, eye, frame)
@@ -165,6 +166,7 @@ struct RectifyArgs {
     int persistent_ctas;               // > 0: persistent pipelined kernel with this many CTAs (a multiple of the SM count)
     int batch_loop;                    // > 0 (= SM count): one CTA per (tile, eye) walks a run of frames (rectify_batch_kernel)
     int bulk_copy;                     // 1: stage the footprints with TMA tensor copies + mbarriers (rectify_tma_kernel) when alignment allows
+    int no_fixed_size;                 // batch kernel: do not use the 640x480 instantiation (tests, tuning)
     int force_unaligned;               // batch kernel: take the 2-byte-aligned code path even for 4-byte aligned frames (tests, tuning)
     int l2_prefetch;                   // batch kernel: prefetch.global.L2 of the frame this many iterations ahead (0 = off, < 0 = automatic)
     int box_w, box_h;                  // largest staged footprint of the calibration over full tiles (pixels, rows), both eyes

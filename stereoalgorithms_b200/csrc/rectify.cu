@@ -452,7 +452,11 @@ __global__ void __launch_bounds__(kRectThreads, 4) rectify_persistent_kernel(con
 // aligned words and funnel-shifted by the address's low bits, rectified bytes leave as byte stores.
 // PART: the tile reaches past the right/bottom image edge; its out-of-image pixels are masked.  Kept out of the common
 // instantiation: the extra predicates cost ~15 % there.
-template <int DTYPE, bool IDENT, bool WRITE_TENSOR, bool A4, bool PART>
+// FW, FH: compile-time image size (0 = run-time).  With the size fixed every per-pixel output offset - 4 rows x 3 planes of
+// tensor stores, 4 rows of rectified words - becomes an immediate of ONE base register that advances once per frame,
+// instead of a 64-bit multiply-add per store: ~30 of 257 instructions per warp and frame.  Instantiated for 640x480, the
+// only size the reference accepts (TRTFastACVNet_plus.cpp:121-122).
+template <int DTYPE, bool IDENT, bool WRITE_TENSOR, bool A4, bool PART, int FW = 0, int FH = 0>
 __device__ __forceinline__ void rectify_batch_body(const RectifyArgs& a, int tiles_x, int out_align, int frames_per_cta, uint32_t (*s_src2)[kFootprintWords],
                                                    typename TensorT<DTYPE>::type* s_lut)
 {
@@ -461,7 +465,7 @@ __device__ __forceinline__ void rectify_batch_body(const RectifyArgs& a, int til
     uint32_t* const s_out = s_src2[1];                               // only the generic path needs s_out; it never overlaps the loop below
 
     const int tid = threadIdx.x;
-    const int W = a.W, H = a.H;
+    const int W = FW ? FW : a.W, H = FH ? FH : a.H;
     const int eye = blockIdx.z & 1, chunk = blockIdx.z >> 1;
     const int f0 = chunk * frames_per_cta;
     int f1 = min(a.n, f0 + frames_per_cta);
@@ -646,7 +650,7 @@ __device__ __forceinline__ void rectify_batch_body(const RectifyArgs& a, int til
     }
 }
 
-template <int DTYPE, bool IDENT, bool WRITE_TENSOR, bool A4>
+template <int DTYPE, bool IDENT, bool WRITE_TENSOR, bool A4, int FW = 0, int FH = 0>
 __global__ void __launch_bounds__(kRectThreads, SA_BATCH_MINB) rectify_batch_kernel(const RectifyArgs a, int tiles_x, int out_align, int frames_per_cta)
 {
     using T = typename TensorT<DTYPE>::type;
@@ -655,6 +659,11 @@ __global__ void __launch_bounds__(kRectThreads, SA_BATCH_MINB) rectify_batch_ker
     if (!IDENT) {
         const T* lut = static_cast<const T*>(a.lut);
         for (int i = threadIdx.x; i < 768; i += kRectThreads) s_lut[i] = lut[i];
+    }
+    if (FW) {                                                        // fixed sizes are multiples of the tile: no partial tiles
+        static_assert(FW % kTileW == 0 && FH % kTileH == 0, "fixed-size instantiation needs whole tiles");
+        rectify_batch_body<DTYPE, IDENT, WRITE_TENSOR, A4, false, FW, FH>(a, tiles_x, out_align, frames_per_cta, s_src2, s_lut);
+        return;
     }
     const bool full = (int)(blockIdx.x + 1) * kTileW <= a.W && (int)(blockIdx.y + 1) * kTileH <= a.H;
     if (full) rectify_batch_body<DTYPE, IDENT, WRITE_TENSOR, A4, false>(a, tiles_x, out_align, frames_per_cta, s_src2, s_lut);
@@ -921,7 +930,8 @@ cudaError_t launch_rectify_t(const RectifyArgs& a, bool aligned4, int tiles_x, i
                     return cudaGetLastError();
                 }
             }
-            if (a4) rectify_batch_kernel<DTYPE, IDENT, WT, true><<<g, kRectThreads, 0, s>>>(a, tiles_x, out_align, fpc);
+            if (a4 && a.W == 640 && a.H == 480 && !a.no_fixed_size) rectify_batch_kernel<DTYPE, IDENT, WT, true, 640, 480><<<g, kRectThreads, 0, s>>>(a, tiles_x, out_align, fpc);
+            else if (a4) rectify_batch_kernel<DTYPE, IDENT, WT, true><<<g, kRectThreads, 0, s>>>(a, tiles_x, out_align, fpc);
             else rectify_batch_kernel<DTYPE, IDENT, WT, false><<<g, kRectThreads, 0, s>>>(a, tiles_x, out_align, fpc);
             return cudaGetLastError();
         }

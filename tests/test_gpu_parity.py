@@ -82,7 +82,7 @@ def test_maps_absurd_calibrations(golden, calibs, tag):
 # ---- a3: rectified images -------------------------------------------------------------------------------------
 @pytest.mark.parametrize("name", ["calib_a", "calib_b", "calib_c_rational"])
 @pytest.mark.parametrize("variant", ["default", "tile_fastest", "force_direct", "force_generic", "persistent", "persistent_tile_fastest", "per_tile_cta", "no_bulk", "force_unaligned",
-                                     "no_l2_prefetch"])
+                                     "no_l2_prefetch", "no_fixed_size"])
 def test_rectified_demo_bit_exact(golden, demo_pair, name, variant):
     g_ = golden["cases"]["demo_" + name]
     l, r = demo_pair
@@ -102,6 +102,8 @@ def test_rectified_demo_bit_exact(golden, demo_pair, name, variant):
             g.set_option("force_unaligned", 1)       # the W % 4 != 0 code path (funnel-shifted loads, run-wise word stores) on aligned frames
         if variant == "no_l2_prefetch":
             g.set_option("l2_prefetch", 0)
+        if variant == "no_fixed_size":
+            g.set_option("no_fixed_size", 1)          # the run-time-size instantiation of the batch kernel at 640x480
         if variant == "force_generic":
             g.set_option("force_generic", 1)
         g.load_calibration_yaml(os.path.join(GOLDEN, name + ".yml"))
@@ -491,7 +493,7 @@ def test_rectified_unaligned_widths_batches(calibs, size, l2_prefetch):
 
 
 @pytest.mark.parametrize("ctas_per_sm", [1, 16, 1000])
-@pytest.mark.parametrize("bulk", [1, 0])
+@pytest.mark.parametrize("bulk", [1, 0, -1])
 def test_rectified_long_batches_all_chunkings(calibs, demo_pair, ctas_per_sm, bulk):
     """The batch-loop kernel with many frames per CTA (register prefetch of f+1, L2 prefetch of f+2, both shared-memory
     buffers in rotation), with the default chunking, and with one frame per CTA; tensors checked too."""
@@ -504,7 +506,8 @@ def test_rectified_long_batches_all_chunkings(calibs, demo_pair, ctas_per_sm, bu
     lut = O.norm_lut(O.FASTACVNET_PLUS)
     with geom(640, 480, model="FastACVNet_plus", max_batch=n) as g:
         g.set_option("batch_ctas", ctas_per_sm)
-        g.set_option("bulk", bulk)
+        g.set_option("bulk", max(bulk, 0))
+        g.set_option("no_fixed_size", 1 if bulk < 0 else 0)        # -1: the batch kernel's run-time-size instantiation
         g.set_calibration(c)
         g.rectify_preprocess(L, R)
         gl, gr, tl = g.rectified(n, 0), g.rectified(n, 1), g.tensor(n, 0)
