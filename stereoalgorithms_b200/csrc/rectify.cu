@@ -447,6 +447,12 @@ __global__ void __launch_bounds__(kRectThreads, 4) rectify_persistent_kernel(con
 #define SA_BATCH_MINB 4
 #endif
 
+// prefetch.global.L2 of `p` if off >= 0, as ONE predicated instruction (a branch around it costs more than the prefetch)
+__device__ __forceinline__ void l2_prefetch_if(const void* p, int off)
+{
+    asm volatile("{\n.reg .pred q;\nsetp.ge.s32 q, %1, 0;\n@q prefetch.global.L2 [%0];\n}\n" ::"l"(p), "r"(off));
+}
+
 // A4: every input row and every rectified row starts on a 4-byte boundary and W is a multiple of 4 (640, 1920, 3840 ...).
 // !A4 (e.g. 1242-wide frames, whose rows and frames are only 2-byte aligned): source words are loaded from the enclosing
 // aligned words and funnel-shifted by the address's low bits, rectified bytes leave as byte stores.
@@ -594,6 +600,7 @@ __device__ __forceinline__ void rectify_batch_body(const RectifyArgs& a, int til
     fetch(src);
     // frames ahead (0 = off); automatic: 2, but off on the 2-byte-aligned path (measured 3 % slower there, 9 % faster elsewhere)
     const int pfd = a.l2_prefetch >= 0 ? a.l2_prefetch : (A4 ? 2 : 0);
+    const uint8_t* pf = src + (size_t)pfd * a.src_frame;              // frame f + pfd, advanced with the loop
 
     for (int f = f0; f < f1; f++) {
         uint32_t* const buf = s_src2[(f - f0) & 1];
@@ -602,12 +609,12 @@ __device__ __forceinline__ void rectify_batch_body(const RectifyArgs& a, int til
         if (third) store_slot(buf, 2);
         __syncthreads();      // the only barrier of the iteration: the other buffer was last read before the previous one
         if (f + 1 < f1) { src += a.src_frame; fetch(src); }            // next frame's words fly during this frame's blend
-        if (pfd && f + pfd < f1) {                                      // and a later frame is pulled into L2, so that
-            const uint8_t* nxt = src + (size_t)(pfd - 1) * a.src_frame;   // its fetch is an L2 hit, not a DRAM round trip
-            if (soff[0] >= 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(nxt + soff[0]));
-            if (soff[1] >= 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(nxt + soff[1]));
-            if (third && soff[2] >= 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(nxt + soff[2]));
+        if (pfd && f + pfd < f1) {                                      // and a later frame is pulled into L2, so that its fetch
+            l2_prefetch_if(pf + soff[0], soff[0]);                      // is an L2 hit, not a DRAM round trip
+            l2_prefetch_if(pf + soff[1], soff[1]);
+            if (third) l2_prefetch_if(pf + soff[2], soff[2]);
         }
+        pf += a.src_frame;
 
         const char* sb = reinterpret_cast<const char*>(buf);
 #pragma unroll
