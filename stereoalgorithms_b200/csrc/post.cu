@@ -48,6 +48,10 @@ __global__ void __launch_bounds__(256) minmax_kernel(const float* __restrict__ d
 
 // ---- heatmap: heatmap() of FastACVNet_plus/test/main.cpp:7-24 -------------------------------------------------
 //   s = f32((max-min)/255)  [double arithmetic];  n = f32(f32(d - f32(min)) / s);  idx = sat_u8(round_half_even(|n|))
+// One CTA colours kHeatIters x 1024 pixels: the JET table is staged once per CTA, and all of a thread's disparity loads are
+// issued before the first one is used.
+constexpr int kHeatIters = 4;
+
 template <bool VEC>
 __global__ void __launch_bounds__(256) heatmap_kernel(const float* __restrict__ disp, size_t disp_frame, int npix, const unsigned* __restrict__ minmax,
                                                       uint8_t* __restrict__ out)
@@ -56,45 +60,55 @@ __global__ void __launch_bounds__(256) heatmap_kernel(const float* __restrict__ 
     __shared__ uint32_t s_w[8][96];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     s_jet[tid] = c_jet[tid];
-    __syncthreads();
     const int frame = blockIdx.y;
     const float mn = dec_ordered(minmax[2 * frame]), mx = dec_ordered(~minmax[2 * frame + 1]);
     const float s = (float)(((double)mx - (double)mn) / 255.0);
     const float* d = disp + (size_t)frame * disp_frame;
     uint8_t* o = out + (size_t)frame * npix * 3;
-    const int p0 = (blockIdx.x * 256 + tid) * 4;
-    uint32_t px[4];
-    float v[4] = {0.f, 0.f, 0.f, 0.f};
-    if (VEC) { if (p0 < npix) { const float4 t = *reinterpret_cast<const float4*>(d + p0); v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w; } }
-    else { for (int k = 0; k < 4; k++) if (p0 + k < npix) v[k] = d[p0 + k]; }
+    float v[kHeatIters][4];
 #pragma unroll
-    for (int k = 0; k < 4; k++) {
-        const float n = fabsf(__fdiv_rn(__fsub_rn(v[k], mn), s));
-        int idx = __float2int_rn(n);            // NaN -> 0, like saturate_cast<uchar>(cvRound(NaN) = INT_MIN)
-        idx = min(255, max(0, idx));
-        px[k] = s_jet[idx];
+    for (int it = 0; it < kHeatIters; it++) {
+        const int p0 = ((blockIdx.x * kHeatIters + it) * 256 + tid) * 4;
+        v[it][0] = v[it][1] = v[it][2] = v[it][3] = 0.f;
+        if (VEC) { if (p0 < npix) { const float4 t = *reinterpret_cast<const float4*>(d + p0); v[it][0] = t.x; v[it][1] = t.y; v[it][2] = t.z; v[it][3] = t.w; } }
+        else { for (int k = 0; k < 4; k++) if (p0 + k < npix) v[it][k] = d[p0 + k]; }
     }
-    if (VEC) {
-        // 12 bytes per lane -> three coalesced 4-byte stores per lane through a warp-private transpose
-        uint32_t* sw = s_w[warp];
-        sw[lane * 3 + 0] = px[0] | (px[1] << 24);
-        sw[lane * 3 + 1] = (px[1] >> 8) | (px[2] << 16);
-        sw[lane * 3 + 2] = (px[2] >> 16) | (px[3] << 8);
-        __syncwarp();
-        const size_t w0 = (size_t)(blockIdx.x * 256 + warp * 32) * 3;   // first word of this warp
-        const size_t nwords = (size_t)npix * 3 / 4;
-        uint32_t* ow = reinterpret_cast<uint32_t*>(o);
+    __syncthreads();
 #pragma unroll
-        for (int m = 0; m < 3; m++) {
-            const size_t wi = w0 + lane + 32 * m;
-            if (wi < nwords) ow[wi] = sw[lane + 32 * m];
+    for (int it = 0; it < kHeatIters; it++) {
+        const int chunk = blockIdx.x * kHeatIters + it;
+        const int p0 = (chunk * 256 + tid) * 4;
+        uint32_t px[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const float n = fabsf(__fdiv_rn(__fsub_rn(v[it][k], mn), s));
+            int idx = __float2int_rn(n);            // NaN -> 0, like saturate_cast<uchar>(cvRound(NaN) = INT_MIN)
+            idx = min(255, max(0, idx));
+            px[k] = s_jet[idx];
         }
-    } else {
-        for (int k = 0; k < 4; k++)
-            if (p0 + k < npix) {
-                uint8_t* q = o + (size_t)(p0 + k) * 3;
-                q[0] = (uint8_t)px[k]; q[1] = (uint8_t)(px[k] >> 8); q[2] = (uint8_t)(px[k] >> 16);
+        if (VEC) {
+            // 12 bytes per lane -> three coalesced 4-byte stores per lane through a warp-private transpose
+            uint32_t* sw = s_w[warp];
+            sw[lane * 3 + 0] = px[0] | (px[1] << 24);
+            sw[lane * 3 + 1] = (px[1] >> 8) | (px[2] << 16);
+            sw[lane * 3 + 2] = (px[2] >> 16) | (px[3] << 8);
+            __syncwarp();
+            const size_t w0 = (size_t)(chunk * 256 + warp * 32) * 3;   // first word of this warp
+            const size_t nwords = (size_t)npix * 3 / 4;
+            uint32_t* ow = reinterpret_cast<uint32_t*>(o);
+#pragma unroll
+            for (int m = 0; m < 3; m++) {
+                const size_t wi = w0 + lane + 32 * m;
+                if (wi < nwords) ow[wi] = sw[lane + 32 * m];
             }
+            __syncwarp();                                               // sw is rewritten by the next chunk
+        } else {
+            for (int k = 0; k < 4; k++)
+                if (p0 + k < npix) {
+                    uint8_t* q = o + (size_t)(p0 + k) * 3;
+                    q[0] = (uint8_t)px[k]; q[1] = (uint8_t)(px[k] >> 8); q[2] = (uint8_t)(px[k] >> 16);
+                }
+        }
     }
 }
 
@@ -205,7 +219,7 @@ cudaError_t launch_heatmap(const float* disp, size_t disp_frame, int npix, int n
 {
     if (n <= 0) return cudaSuccess;
     const bool vec = (npix % 4 == 0) && (disp_frame % 4 == 0) && (((uintptr_t)disp) % 16 == 0) && (((uintptr_t)out) % 4 == 0);
-    dim3 grid((unsigned)((npix + 1023) / 1024), (unsigned)n);
+    dim3 grid((unsigned)((npix + 1024 * kHeatIters - 1) / (1024 * kHeatIters)), (unsigned)n);
     if (vec) heatmap_kernel<true><<<grid, 256, 0, s>>>(disp, disp_frame, npix, minmax, out);
     else heatmap_kernel<false><<<grid, 256, 0, s>>>(disp, disp_frame, npix, minmax, out);
     if (launches) ++*launches;
