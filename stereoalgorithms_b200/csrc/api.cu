@@ -168,7 +168,7 @@ static int stage_rectify(sa_handle* h, int f0, int n, const uint8_t* src_l, cons
                          cudaStream_t s)
 {
     // src_l / src_r point at frame f0 already
-    const size_t rect_frame = (size_t)h->W * h->H * 3;
+    const size_t rect_frame = h->rect_frame;
     const size_t tplane = (size_t)h->w * h->h;
     const bool hit = h->cfg.model == SA_MODEL_HITNET;
     const size_t tframe = hit ? 6 * tplane : 3 * tplane;
@@ -187,6 +187,7 @@ static int stage_rectify(sa_handle* h, int f0, int n, const uint8_t* src_l, cons
         for (int e = 0; e < 2; e++) { a.map1[e] = h->map1[e]; a.map2[e] = h->map2[e]; a.tiles[e] = h->tiles[e]; a.tmap[e] = h->tmap[e]; }
         a.lut = lut;
         a.src_pitch = pitch; a.src_frame = frame_bytes; a.tensor_frame = tframe;
+        a.rect_pitch = h->rect_pitch; a.rect_frame = h->rect_frame;
         a.W = h->W; a.H = h->H; a.n = n; a.model = h->cfg.model; a.dtype = h->cfg.tensor_dtype;
         a.write_tensor = h->resize ? 0 : 1;
         a.frame_fastest = (int)h->opt_frame_fastest;
@@ -204,7 +205,7 @@ static int stage_rectify(sa_handle* h, int f0, int n, const uint8_t* src_l, cons
             SA_CUDA(h, launch_rectify(a, s, &h->launches));
         }
         net_src[0] = a.rect[0]; net_src[1] = a.rect[1];
-        net_pitch = (size_t)h->W * 3; net_frame = rect_frame;
+        net_pitch = h->rect_pitch; net_frame = rect_frame;
     } else {
         net_src[0] = src_l; net_src[1] = src_r;
         net_pitch = pitch; net_frame = frame_bytes;
@@ -340,9 +341,15 @@ int sa_create(const sa_config* cfg, sa_handle** out)
     A(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
     A(cudaStreamCreateWithFlags(&h->s_h2d, cudaStreamNonBlocking));
     A(cudaStreamCreateWithFlags(&h->s_d2h, cudaStreamNonBlocking));
+    // rectified rows: dense when W is a multiple of 4 (12-byte pixel groups then tile every row); otherwise padded so that
+    // every row starts 16-byte aligned and ends on a whole group - the kernels' packed word stores need that, and byte
+    // stores into 2-byte-aligned rows cost 1242-wide frames 20 % of stage A.  Readers get the pitch (colour source of stage
+    // B, resize, sa_copy_rectified).
+    h->rect_pitch = h->W % 4 == 0 ? (size_t)h->W * 3 : ((size_t)((h->W + 3) / 4) * 12 + 15) / 16 * 16;
+    h->rect_frame = h->rect_pitch * h->H;
     for (int eye = 0; eye < 2 && ok; eye++) {
         A(dev_alloc(&h->raw[eye], N * img));
-        A(dev_alloc(&h->rect[eye], N * img));
+        A(dev_alloc(&h->rect[eye], N * h->rect_frame));
         if (h->resize) A(dev_alloc(&h->net_u8[eye], N * npix * 3));
         A(dev_alloc(&h->map1[eye], mpix));
         A(dev_alloc(&h->map2[eye], mpix));
@@ -741,7 +748,7 @@ int sa_copy_rectified(sa_handle* h, int n, int eye, uint8_t* out, int where, sa_
     if (!src) return fail(h, SA_ERR_NOT_READY, "sa_copy_rectified: nothing processed yet");
     cudaStream_t s = pick(h, stream);
     const size_t row = (size_t)h->W * 3;
-    const size_t pitch = h->resize ? row : h->color_pitch;
+    const size_t pitch = h->resize ? h->rect_pitch : h->color_pitch;
     SA_CUDA(h, cudaMemcpy2DAsync(out, row, src, pitch, row, (size_t)n * h->H, where == SA_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, s));
     if (where == SA_HOST) SA_CUDA(h, cudaStreamSynchronize(s));
     return SA_OK;
@@ -857,7 +864,7 @@ int sa_run_batch(sa_handle* h, int n, const uint8_t* left, const uint8_t* right,
         if (disparity) SA_CUDA(h, cudaMemcpy2DAsync(disparity + (size_t)f0 * npix, npix * sizeof(float), h->disp + (size_t)f0 * dfl, dfl * sizeof(float), npix * sizeof(float), (size_t)m, cudaMemcpyDeviceToHost, h->s_d2h));
         if (rectify)
             for (int e = 0; e < 2; e++)
-                if (rect_out[e]) SA_CUDA(h, cudaMemcpyAsync(rect_out[e] + (size_t)f0 * img, h->rect[e] + (size_t)f0 * img, (size_t)m * img, cudaMemcpyDeviceToHost, h->s_d2h));
+                if (rect_out[e]) SA_CUDA(h, cudaMemcpy2DAsync(rect_out[e] + (size_t)f0 * img, (size_t)h->W * 3, h->rect[e] + (size_t)f0 * h->rect_frame, h->rect_pitch, (size_t)h->W * 3, (size_t)m * h->H, cudaMemcpyDeviceToHost, h->s_d2h));
         if (heatmap) SA_CUDA(h, cudaMemcpyAsync(heatmap + (size_t)f0 * npix * 3, h->heat + (size_t)f0 * npix * 3, (size_t)m * npix * 3, cudaMemcpyDeviceToHost, h->s_d2h));
     }
     // colour / rectified pointers describe frame 0 of the whole batch

@@ -75,6 +75,8 @@ struct sa_handle {
     uint16_t* map2[2] = {nullptr, nullptr};
     sa::TileInfo* tiles[2] = {nullptr, nullptr};
     uint32_t* tmap[2] = {nullptr, nullptr};   // derived per-pixel table of the fast rectify path, [H][W]
+    size_t rect_pitch = 0, rect_frame = 0;    // rectified rows: 3 W bytes when W % 4 == 0, else 3 * roundup(W, 4) rounded up to 16 bytes, so
+                                              // that every row starts 16-byte aligned and holds whole 4-pixel (12-byte) groups
     int* fp_max = nullptr;                    // device: {max footprint width, height} over staged full tiles of both eyes
     int box_w = 0, box_h = 0;                 // host copy of fp_max
     float* lut32 = nullptr;                   // [3][256]
@@ -167,6 +169,7 @@ struct RectifyArgs {
     int batch_loop;                    // > 0 (= SM count): one CTA per (tile, eye) walks a run of frames (rectify_batch_kernel)
     int bulk_copy;                     // 1: stage the footprints with TMA tensor copies + mbarriers (rectify_tma_kernel) when alignment allows
     int no_fixed_size;                 // batch kernel: do not use the 640x480 instantiation (tests, tuning)
+    size_t rect_pitch, rect_frame;     // bytes per row / per frame of the rectified output (rows padded, see sa_handle::rect_pitch)
     int force_unaligned;               // batch kernel: take the 2-byte-aligned code path even for 4-byte aligned frames (tests, tuning)
     int l2_prefetch;                   // batch kernel: prefetch.global.L2 of the frame this many iterations ahead (0 = off, < 0 = automatic)
     int box_w, box_h;                  // largest staged footprint of the calibration over full tiles (pixels, rows), both eyes

@@ -89,6 +89,13 @@ __device__ __forceinline__ void blend(uint32_t p00, uint32_t p01, uint32_t p10, 
 #endif
 }
 
+// First word a lane stores of the rectified row `row` (bytes per row = pitch, a multiple of 4): lanes m = 0..2 of every
+// group of four pixels write the three words of the group's 12 bytes.
+__device__ __forceinline__ uint32_t* rect_words(uint8_t* frame_base, size_t pitch, int row, int x, int m)
+{
+    return reinterpret_cast<uint32_t*>(frame_base + (size_t)row * pitch) + (3 * ((x - m) >> 2) + m);
+}
+
 template <int DTYPE, bool IDENT, typename T>
 __device__ __forceinline__ void normalise(const T* s_lut, uint32_t vB, uint32_t vG, uint32_t vR, T& r, T& g, T& b)
 {
@@ -179,9 +186,9 @@ __device__ __forceinline__ void tile_fast(const RectifyArgs& a, const TileInfo t
     const int plane = W * a.H;
     const int m = tid & 3;
     const uint32_t sel = m == 0 ? 0x4210u : (m == 1 ? 0x5421u : 0x6542u);
-    uint32_t* __restrict__ rp = reinterpret_cast<uint32_t*>(a.rect[eye] + (size_t)frame * plane * 3) + (3 * ((pix0 - m) >> 2) + m);
+    uint32_t* __restrict__ rp = rect_words(a.rect[eye] + (size_t)frame * a.rect_frame, a.rect_pitch, ty0 + (tid >> 6), tx0 + (tid & (kTileW - 1)), m);
     T* __restrict__ tp = WRITE_TENSOR ? static_cast<T*>(a.tensor[eye]) + (size_t)frame * a.tensor_frame + pix0 : nullptr;
-    const int wstep = 3 * W;
+    const int wstep = (int)a.rect_pitch;                             // words per 4 rows
 #pragma unroll
     for (int k = 0; k < 4; k++) {
         const uint32_t t = tm[k];
@@ -266,8 +273,8 @@ __device__ __forceinline__ void tile_generic(const RectifyArgs& a, const TileInf
 
     // rectified BGR tile -> global, widest stores the alignment allows
     const int rows = min(kTileH, H - ty0), row_bytes = min(kTileW, W - tx0) * 3;
-    uint8_t* g = (eye ? a.rect[1] : a.rect[0]) + (size_t)frame * plane * 3 + ((size_t)ty0 * W + tx0) * 3;
-    const size_t gpitch = (size_t)W * 3;
+    uint8_t* g = (eye ? a.rect[1] : a.rect[0]) + (size_t)frame * a.rect_frame + (size_t)ty0 * a.rect_pitch + (size_t)tx0 * 3;
+    const size_t gpitch = a.rect_pitch;
     if (out_align >= 16) copy_rows<uint4>(g, gpitch, s_out_b, rows, row_bytes);
     else if (out_align >= 4) copy_rows<uint32_t>(g, gpitch, s_out_b, rows, row_bytes);
     else if (out_align >= 2) copy_rows<uint16_t>(g, gpitch, s_out_b, rows, row_bytes);
@@ -337,7 +344,7 @@ __global__ void __launch_bounds__(kRectThreads, 4) rectify_persistent_kernel(con
     auto tile_fast_ok = [&](const TileInfo& t, int x, int y) { return t.w > 0 && x * kTileW + kTileW <= W && y * kTileH + kTileH <= H; };
 
     const int pitch = (int)a.src_pitch;
-    const int rstep = 4 * W, wstep = 3 * W, plane = W * H;
+    const int rstep = 4 * W, wstep = (int)a.rect_pitch, plane = W * H;
     const int m = tid & 3;
     const uint32_t sel = m == 0 ? 0x4210u : (m == 1 ? 0x5421u : 0x6542u);
     const int lpix = (tid >> 6) * W + (tid & (kTileW - 1));     // pixel offset of this thread inside a tile
@@ -403,7 +410,7 @@ __global__ void __launch_bounds__(kRectThreads, 4) rectify_persistent_kernel(con
 
             const int fw = ti_c.w;
             const int pix0 = ty0 * W + tx0 + lpix;
-            uint32_t* __restrict__ rp = reinterpret_cast<uint32_t*>(a.rect[eye] + (size_t)frame * plane * 3) + (3 * ((pix0 - m) >> 2) + m);
+            uint32_t* __restrict__ rp = rect_words(a.rect[eye] + (size_t)frame * a.rect_frame, a.rect_pitch, ty0 + (tid >> 6), tx0 + (tid & (kTileW - 1)), m);
             T* __restrict__ tp = WRITE_TENSOR ? static_cast<T*>(a.tensor[eye]) + (size_t)frame * a.tensor_frame + pix0 : nullptr;
 #pragma unroll
             for (int k = 0; k < 4; k++) {
@@ -504,7 +511,9 @@ __device__ __forceinline__ void rectify_batch_body(const RectifyArgs& a, int til
 
     // ---- per-calibration state of this thread (frame independent) ----------------------------------------------
     const int pix0 = (ty0 + (tid >> 6)) * W + tx0 + (tid & (kTileW - 1));
-    const int rstep = 4 * W, wstep = 3 * W, plane = W * H;
+    const int rstep = 4 * W, plane = W * H;
+    const size_t rect_pitch = FW ? (size_t)3 * FW : a.rect_pitch, rect_frame = FW ? (size_t)3 * FW * FH : a.rect_frame;
+    const int wstep = (int)rect_pitch;                                // words per 4 rows of the rectified image
     uint32_t pvalid = 0xfu;             // bit k: pixel k of this thread lies inside the image
     if (PART) {
         pvalid = 0;
@@ -546,10 +555,12 @@ __device__ __forceinline__ void rectify_batch_body(const RectifyArgs& a, int til
     uint32_t sel = m == 0 ? 0x4210u : (m == 1 ? 0x5421u : 0x6542u);
     asm volatile("" : "+r"(sel));       // keep it in a register: recomputing the selects inside the frame loop costs 5 instructions per pixel
     const uint8_t* __restrict__ src = a.src[eye] + (size_t)f0 * a.src_frame;
-    uint32_t* __restrict__ rp = reinterpret_cast<uint32_t*>(a.rect[eye] + (size_t)f0 * plane * 3) + (3 * ((pix0 - m) >> 2) + m);   // A4
-    uint8_t* __restrict__ rb = a.rect[eye] + (size_t)f0 * plane * 3 + (size_t)pix0 * 3;                                              // !A4
+    // The rectified buffer is internal and its rows are padded to 4-pixel groups on 4-byte boundaries (sa_handle::rect_pitch),
+    // so the packed word stores below work for every width; lanes of a group that straddles x = W write their neighbour's
+    // (unused) bytes into the row padding.
+    uint32_t* __restrict__ rp = rect_words(a.rect[eye] + (size_t)f0 * rect_frame, rect_pitch, ty0 + (tid >> 6), tx0 + (tid & (kTileW - 1)), m);
     T* __restrict__ tp = WRITE_TENSOR ? static_cast<T*>(a.tensor[eye]) + (size_t)f0 * a.tensor_frame + pix0 : nullptr;
-    const size_t rect_frame_words = (size_t)plane * 3 / 4;
+    const size_t rect_frame_words = rect_frame / 4;
 
     // Raw source words of the next frame.  Slots that have nothing to load (outside the image, or beyond the footprint)
     // stay zero for the whole loop: they are cleared once here and never written again.
@@ -635,19 +646,11 @@ __device__ __forceinline__ void rectify_batch_body(const RectifyArgs& a, int til
             const uint32_t vB = __dp2a_hi(__byte_perm(tB, bB, 0x5410), wt, 512u) >> 10;
             const uint32_t vG = __dp2a_hi(__byte_perm(tG, bG, 0x5410), wt, 512u) >> 10;
             const uint32_t vR = __dp2a_hi(__byte_perm(tR, bR, 0x5410), wt, 512u) >> 10;
-            const bool pv = !PART || ((pvalid >> k) & 1u);             // W % 4 == 0 under A4: the 4 lanes of a packed group agree on it
-            if (A4) {
+            const bool pv = !PART || ((pvalid >> k) & 1u);
+            {
                 const uint32_t v = vB | (vG << 8) | (vR << 16);
                 const uint32_t nb = __shfl_down_sync(0xffffffffu, v, 1);
                 if (m < 3 && pv) rp[k * wstep] = __byte_perm(v, nb, sel);
-            } else if (pv) {
-                // Byte stores.  Two word-packed variants were tried and both measured SLOWER on 256 pairs of 1242x375 (rows
-                // only 2-byte aligned): lane roles rotated by the row's misalignment (1.58 vs 1.47 ms), and run-wise aligned
-                // words chosen per lane from the address's low bits with bytewise run ends (1.58 vs 1.34 ms).  This path is
-                // latency-bound, not issue-bound (issue slots 32 % busy): the shuffle + selector arithmetic lengthens the
-                // per-frame dependency chain more than the saved store instructions shorten it.
-                uint8_t* q = rb + (size_t)k * rstep * 3;
-                q[0] = (uint8_t)vB; q[1] = (uint8_t)vG; q[2] = (uint8_t)vR;
             }
             if (WRITE_TENSOR && pv) {
                 T r, g, b;
@@ -655,7 +658,7 @@ __device__ __forceinline__ void rectify_batch_body(const RectifyArgs& a, int til
                 tp[k * rstep] = r; tp[k * rstep + plane] = g; tp[k * rstep + 2 * plane] = b;
             }
         }
-        if (A4) rp += rect_frame_words; else rb += (size_t)plane * 3;
+        rp += rect_frame_words;
         if (WRITE_TENSOR) tp += a.tensor_frame;
     }
 }
@@ -794,9 +797,9 @@ __global__ void __launch_bounds__(kRectThreads, SA_TMA_MINB)
     const int m = tid & 3;
     uint32_t sel = m == 0 ? 0x4210u : (m == 1 ? 0x5421u : 0x6542u);
     asm volatile("" : "+r"(sel));
-    uint32_t* __restrict__ rp = reinterpret_cast<uint32_t*>(a.rect[eye] + (size_t)f0 * plane * 3) + (3 * ((pix0 - m) >> 2) + m);
+    uint32_t* __restrict__ rp = rect_words(a.rect[eye] + (size_t)f0 * a.rect_frame, a.rect_pitch, ty0 + (tid >> 6), tx0 + (tid & (kTileW - 1)), m);
     T* __restrict__ tp = WRITE_TENSOR ? static_cast<T*>(a.tensor[eye]) + (size_t)f0 * a.tensor_frame + pix0 : nullptr;
-    const size_t rect_frame_words = (size_t)plane * 3 / 4;
+    const size_t rect_frame_words = a.rect_frame / 4;
     const int nf = f1 - f0;
     const int roww = bw;                                                // words per staged row
 
@@ -981,7 +984,7 @@ cudaError_t launch_rectify(const RectifyArgs& a, cudaStream_t s, long* launches)
     // input alignment: every row of every frame of both eyes starts on a 4-byte boundary
     const bool aligned4 = min3(ptr_align(a.src[0]), ptr_align(a.src[1]), min3(size_align(a.src_pitch), size_align(a.src_frame), 256)) >= 4;
     // output alignment of the rectified rows (tile x offsets are multiples of 192 bytes)
-    const int out_align = min3(ptr_align(a.rect[0]), ptr_align(a.rect[1]), min3(size_align((size_t)a.W * 3), size_align((size_t)a.W * a.H * 3), 256));
+    const int out_align = min3(ptr_align(a.rect[0]), ptr_align(a.rect[1]), min3(size_align(a.rect_pitch), size_align(a.rect_frame), 256));
     // fast path: 4-byte aligned rectified rows and 32-bit offsets inside a frame
     const int fast_ok = (out_align >= 4 && a.W % 4 == 0 && a.src_pitch * (size_t)a.H < (1u << 31) && (size_t)a.W * a.H * 3 < (1u << 30) &&
                          !a.force_generic) ? 1 : 0;

@@ -85,6 +85,17 @@ __device__ __forceinline__ void point_xyz(const Q10& q, float d, float fc, float
 // (float) of byte k of a packed BGRx word without the conversion unit: 2^23 + byte, exactly, minus 2^23
 __device__ __forceinline__ float byte_to_float(uint32_t c, uint32_t sel) { return __uint_as_float(__byte_perm(c, 0x4b000000u, sel)) - 8388608.0f; }
 
+// Pitched colour rows: may the thread's 4 pixels be fetched as 16-byte windows (one per row they touch)?  Each window must end
+// inside the frame's pixel data - a caller's buffer has no slack after the last row.
+__device__ __forceinline__ bool pitched_windows_ok(const ReprojectArgs& a, int p0, int npix, int row0, int col0)
+{
+    if (p0 + 4 > npix) return false;
+    const size_t data_end = (size_t)(a.h - 1) * a.color_pitch + 3 * (size_t)a.w;
+    if ((size_t)row0 * a.color_pitch + 3 * (size_t)col0 + 16 > data_end) return false;
+    if (col0 + 4 > a.w && (size_t)(row0 + 1) * a.color_pitch + 16 > data_end) return false;   // also false when row0 is the last row
+    return true;
+}
+
 // Loads disparity + colour of the thread's 4 pixels.
 //   VEC: disparity 16-byte aligned, colour rows contiguous and 4-byte aligned -> one float4 + three words.
 //   !VEC: scalar disparity loads; colour from the enclosing aligned words, funnel-shifted by the frame's misalignment
@@ -106,6 +117,7 @@ __device__ __forceinline__ void load4(const ReprojectArgs& a, int frame, int p0,
             d[0] = d[1] = d[2] = d[3] = 0.f; c[0] = c[1] = c[2] = c[3] = 0u;
         }
     } else if (a.color_pitch == (size_t)a.w * 3 && p0 + 8 <= npix) {
+        // contiguous rows: the 4 pixels are 12 consecutive bytes, even across a row end
 #pragma unroll
         for (int k = 0; k < 4; k++) d[k] = disp[p0 + k];
         const uintptr_t A = reinterpret_cast<uintptr_t>(color + (size_t)p0 * 3);
@@ -114,6 +126,28 @@ __device__ __forceinline__ void load4(const ReprojectArgs& a, int frame, int p0,
         const uint32_t r0 = __ldg(cp), r1 = __ldg(cp + 1), r2 = __ldg(cp + 2), r3 = __ldg(cp + 3);   // cp + 3 is inside the frame: p0 + 8 <= npix
         const uint32_t u0 = __funnelshift_r(r0, r1, sh), u1 = __funnelshift_r(r1, r2, sh), u2 = __funnelshift_r(r2, r3, sh);
         c[0] = u0; c[1] = __byte_perm(u0, u1, 0x4543); c[2] = __byte_perm(u1, u2, 0x4432); c[3] = u2 >> 8;
+    } else if (a.color_pitch != (size_t)a.w * 3 && pitched_windows_ok(a, p0, npix, row0, col0)) {
+        // pitched rows (the padded rectified buffer of widths that are not a multiple of 4, or a caller's ROI): one 16-byte
+        // window at the group's first pixel and, if the group runs over the row end, a second one at the start of the next
+        // row - both issued before either is used
+#pragma unroll
+        for (int k = 0; k < 4; k++) d[k] = disp[p0 + k];
+        const int n0 = min(4, a.w - col0);                                  // pixels of the group in row0
+        auto window = [&](size_t off, uint32_t o[4]) {
+            const uintptr_t A = reinterpret_cast<uintptr_t>(color + off);
+            const uint32_t al = (uint32_t)A & 3u, sh = al << 3;
+            const uint32_t* cp = reinterpret_cast<const uint32_t*>(A - al);
+            const uint32_t r0 = __ldg(cp), r1 = __ldg(cp + 1), r2 = __ldg(cp + 2), r3 = __ldg(cp + 3);
+            const uint32_t u0 = __funnelshift_r(r0, r1, sh), u1 = __funnelshift_r(r1, r2, sh), u2 = __funnelshift_r(r2, r3, sh);
+            o[0] = u0; o[1] = __byte_perm(u0, u1, 0x4543); o[2] = __byte_perm(u1, u2, 0x4432); o[3] = u2 >> 8;
+        };
+        uint32_t ca[4], cb[4] = {0u, 0u, 0u, 0u};
+        window((size_t)row0 * a.color_pitch + 3 * (size_t)col0, ca);
+        if (n0 < 4) window((size_t)(row0 + 1) * a.color_pitch, cb);
+        c[0] = ca[0];
+        c[1] = n0 > 1 ? ca[1] : cb[0];
+        c[2] = n0 > 2 ? ca[2] : (n0 == 2 ? cb[0] : cb[1]);
+        c[3] = n0 > 3 ? ca[3] : (n0 == 3 ? cb[0] : (n0 == 2 ? cb[1] : cb[2]));
     } else {
         int row = row0, col = col0;
 #pragma unroll

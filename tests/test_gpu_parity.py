@@ -266,6 +266,48 @@ def test_reproject_odd_sizes(calibs, size):
             assert np.array_equal(heat[i], O.heatmap(d[i, 0]))
 
 
+@pytest.mark.parametrize("size", [(1242, 375), (638, 50), (333, 77), (67, 19), (9, 7)])
+@pytest.mark.parametrize("source", ["rectified", "pitched_input"])
+def test_reproject_pitched_colour_rows(calibs, size, source):
+    """Stage B reading colours from rows that are NOT contiguous: the internal rectified buffer of widths that are not a
+    multiple of 4 (rows padded to whole 4-pixel groups), and a caller's pitched image (rectify = 0).  Pixel groups that run
+    over a row end, the last groups of a frame (no slack after the last row) and tiny images take different code paths."""
+    from stereoalgorithms_b200.geometry import COMPACT, DENSE
+    W, H = size
+    s = W / 640
+    c = O.scale_calibration(calibs["calib_a"], s, crop_y=(480 * s - H) / 2)
+    n = 3
+    rng = np.random.default_rng(W + 7 * H)
+    L = rng.integers(0, 256, (n, H, W, 3), dtype=np.uint8)
+    d = rng.normal(20, 15, (n, 1, H, W)).astype(np.float32)
+    d[rng.random(d.shape) < 0.1] = 0
+    with geom(W, H, model="FastACVNet_plus", max_batch=n) as g:
+        g.set_calibration(c)
+        if source == "rectified":
+            g.rectify_preprocess(L, L[::-1].copy())
+            (l1, l2), _ = O.rectify_maps(c, (W, H))
+            colour = np.stack([OC.remap(x, l1, l2) for x in L])
+        else:
+            pitch = 3 * W + 5                                           # odd pitch: rows at every byte alignment
+            Lp = np.zeros((n, H, pitch), np.uint8)
+            Lp[:, :, :3 * W] = L.reshape(n, H, 3 * W)
+            Lp = Lp.reshape(-1)[: (n - 1) * H * pitch + (H - 1) * pitch + 3 * W].copy()   # no slack after the last row
+            import torch
+            Ld = torch.from_numpy(Lp).cuda()                            # device input is read in place, with its pitch
+            g.rectify_preprocess(Ld, Ld, n=n, pitch=pitch, rectify=False)
+            colour = L
+        g.set_disparity(d)
+        pts, _ = g.reproject(n, DENSE)
+        cp, cc = g.reproject(n, COMPACT)
+        for i in range(n):
+            want, _ = O.reproject_dense(O.FASTACVNET_PLUS, d[i, 0], colour[i], c["Q"])
+            assert_close_points(pts[i], want, f"{size} {source} dense")
+            assert np.array_equal(pts[i][:, 3:], want[:, 3:])
+            wc, k, _ = O.reproject_compact(O.FASTACVNET_PLUS, d[i, 0], colour[i], c["Q"])
+            assert cc[i] == k
+            assert np.array_equal(cp[i, :k, 3:], wc[:, 3:])
+
+
 def test_reproject_general_Q(calibs, demo_pair):
     """A Q with every used entry non-trivial: products are no longer exact, hence the 1e-5 gate."""
     from stereoalgorithms_b200.geometry import DENSE
