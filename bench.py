@@ -46,6 +46,8 @@ WORKLOADS = {
 }
 # not BASELINE configs: diagnostic shapes used while tuning the 2-byte-aligned (W % 4 != 0) path
 WORKLOADS.update({
+    # BASELINE configs[3] (ii): 1080p capture, network at 640x480 (rectify at full size -> 8-bit INTER_LINEAR resize -> tensors)
+    "stream_1080p_resize_640x480_b64_f32": dict(model="FastACVNet_plus", W=1920, H=1080, net=(640, 480), batch=64, dtype="f32", calib=("calib_a", 3.0)),
     "exp_1240x375_b256_f32": dict(model="FastACVNet_plus", W=1240, H=375, batch=256, dtype="f32", calib=("calib_a", 1240 / 640)),
     "exp_1242x375_b64_f32": dict(model="FastACVNet_plus", W=1242, H=375, batch=64, dtype="f32", calib=("calib_a", 1242 / 640)),
     "exp_1242x376_b256_f32": dict(model="FastACVNet_plus", W=1242, H=376, batch=256, dtype="f32", calib=("calib_a", 1242 / 640)),
@@ -56,9 +58,12 @@ DEFAULT_WORKLOAD = "raft_realtime_640x480_b64_f16"
 def bytes_per_pair(wl, stage):
     """Algorithmic HBM bytes per stereo pair (SURVEY.md section 8d / DESIGN.md): maps, LUTs and Q are batch-shared
     constants and are not counted."""
-    wh = wl["W"] * wl["H"]
+    WH = wl["W"] * wl["H"]                                     # full-resolution image
+    wh = wl["net"][0] * wl["net"][1] if wl.get("net") else WH  # network / disparity / point-cloud size (= WH unless resizing)
     t = 2 if wl["dtype"] == "f16" else 4
-    a = 2 * 3 * wh + 2 * 3 * wh + 2 * 3 * wh * t              # raw u8 in, rectified u8 out, tensors out (both eyes)
+    # raw u8 in, rectified u8 out, tensors out (both eyes).  With a resize the intermediate traffic (rectified image read
+    # back, resized u8 written and read) is NOT counted: it is not compulsory, a fully fused path would not have it.
+    a = 2 * 3 * WH + 2 * 3 * WH + 2 * 3 * wh * t
     b = 4 * wh + 3 * wh + 24 * wh + (4 * wh if wl["model"] == "RAFTStereo" else 0)   # disparity, left u8, points (+ write-back)
     return {"rectify": a, "reproject": b, "total": a + b}[stage]
 
@@ -283,7 +288,9 @@ def main():
     L, R = make_inputs(wl, n, rank)
     dL, dR = torch.from_numpy(L).cuda(), torch.from_numpy(R).cuda()
 
-    g = StereoGeometry(W, H, model=wl["model"], dtype=F16 if wl["dtype"] == "f16" else F32, max_batch=n, gpu_id=local, flags=SL.FLAG_TIMING)
+    g = StereoGeometry(W, H, model=wl["model"], dtype=F16 if wl["dtype"] == "f16" else F32, max_batch=n, gpu_id=local, flags=SL.FLAG_TIMING,
+                       net_size=wl.get("net"))
+    w, h = wl.get("net") or (W, H)
     g.set_calibration(calib)
     if args.frame_fastest >= 0:
         g.set_option("frame_fastest", args.frame_fastest)
@@ -328,6 +335,10 @@ def main():
     step_time = ev0.elapsed_time(ev1) / 1e3                   # device time of exactly K steps, events on the launch stream
     launches = g.launch_count - launches0
     rect_ms, rect_cnt = g.stage_time(SL.STAGE_RECTIFY)
+    resize_ms = 0.0
+    if wl.get("net"):
+        resize_ms = g.stage_time(SL.STAGE_RESIZE)[0]         # resize + preprocess kernels
+        rect_ms += resize_ms                                  # stage A = rectify + resize + preprocess
     rep_ms, rep_cnt = g.stage_time(SL.STAGE_REPROJECT)
     heat_ms, _ = g.stage_time(SL.STAGE_HEATMAP) if args.heatmap else (0.0, 0)
     dev_ms = rect_ms + rep_ms + heat_ms                      # sum of the per-kernel event pairs
@@ -340,11 +351,11 @@ def main():
     e2e = None
     if not args.no_e2e:
         k2 = args.e2e_steps or min(args.steps, 20)
-        npix = W * H
+        npix = w * h
         hin = [PinnedArray(L.shape, np.uint8), PinnedArray(R.shape, np.uint8)]
         hin[0].array[:] = L
         hin[1].array[:] = R
-        hout = [PinnedArray((n, npix, 6), np.float32), PinnedArray((n, H, W), np.float32), PinnedArray(L.shape, np.uint8), PinnedArray(R.shape, np.uint8)]
+        hout = [PinnedArray((n, npix, 6), np.float32), PinnedArray((n, h, w), np.float32), PinnedArray(L.shape, np.uint8), PinnedArray(R.shape, np.uint8)]
 
         def e2e_step():
             g.run_batch(hin[0].array, hin[1].array, n, rectify=True, stub_seed=0, pointcloud=hout[0].array, disparity=hout[1].array,
@@ -358,8 +369,8 @@ def main():
             e2e_step()                                        # synchronous: returns when the results are in host memory
         el2 = time.perf_counter() - t0
         pairs2, t2, _ = sharding.aggregate(n * k2, el2)
-        h2d = 2 * n * npix * 3
-        d2h = n * npix * (24 + 4 + 6)
+        h2d = 2 * n * W * H * 3
+        d2h = n * (npix * (24 + 4) + W * H * 6)
         e2e = {"value": pairs2 / t2, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "steps": k2,
                "api": "sa_run_batch (pinned host images in; point cloud + disparity + rectified L/R out)",
                "pcie_gbs_per_gpu": (h2d + d2h) * k2 / t2 / 1e9}
@@ -373,11 +384,12 @@ def main():
         dom_ms, dom_cnt = stages[dom]
         per_launch_bytes = bytes_per_pair(wl, dom) * n
         achieved = per_launch_bytes / (dom_ms / dom_cnt * 1e-3) / 1e9
-        roof = {"bound": "hbm", "kernel": "rectify_kernel (fused rectify+preprocess)" if dom == "rectify" else "reproject_dense_kernel",
+        roof = {"bound": "hbm", "kernel": "rectify_batch_kernel (fused rectify+preprocess)" if dom == "rectify" else "reproject_dense_kernel",
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src, "traffic": None,
                 "algorithmic_bytes_per_launch": per_launch_bytes, "avg_launch_ms": dom_ms / dom_cnt,
                 "stages": {k: {"ms_per_launch": v[0] / max(v[1], 1), "GBps": bytes_per_pair(wl, k) * n / (v[0] / max(v[1], 1) * 1e-3) / 1e9,
                                "bytes_per_pair": bytes_per_pair(wl, k)} for k, v in stages.items()},
+                "resize_preprocess_ms_per_step": resize_ms / max(rect_cnt, 1) if wl.get("net") else None,
                 "whole_step": {"GBps": bytes_per_pair(wl, "total") * n * args.steps / step_time / 1e9,
                                "frac": bytes_per_pair(wl, "total") * n * args.steps / step_time / 1e9 / peak}}
         prof = os.path.join(ROOT, "profiles", "traffic.json")
@@ -402,7 +414,7 @@ def main():
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": 1e3 * step_time / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "u8 fixed-point + f32 (%s tensors)" % wl["dtype"], "data": "synthetic",
-                "config": {"workload": wname, "model": wl["model"], "size": [W, H], "pairs_per_gpu_per_step": n, "tensor_dtype": wl["dtype"],
+                "config": {"workload": wname, "model": wl["model"], "size": [W, H], "net_size": [w, h], "pairs_per_gpu_per_step": n, "tensor_dtype": wl["dtype"],
                            "reproject": "dense", "heatmap": bool(args.heatmap), "parallelism": f"frame-sharded x{world}, no collective",
                            "numa_node_rank0": numa,
                            "l2": "working set per step %.0f MB >> 126 MB L2 (no flush needed)" % (bytes_per_pair(wl, "total") * n / 1e6),

@@ -230,6 +230,8 @@ static int stage_rectify(sa_handle* h, int f0, int n, const uint8_t* src_l, cons
         p.src_pitch = (size_t)h->w * 3; p.src_frame = nf; p.tensor_frame = tframe;
         p.W = h->w; p.H = h->h; p.n = n; p.model = h->cfg.model; p.dtype = h->cfg.tensor_dtype;
         StageScope t(h, SA_STAGE_RESIZE, s);
+        // (a fused resize + preprocess kernel - 128 x 8 output pixels per CTA, source rows staged with cp.async - was built
+        // and measured slower on 64 pairs 1080p -> 640x480: 0.54 vs 0.43 ms for these two launches; it was removed)
         SA_CUDA(h, launch_resize(r, s, &h->launches));
         SA_CUDA(h, launch_preprocess(p, s, &h->launches));
         if (f0 == 0) { h->color_src[0] = h->net_u8[0]; h->color_src[1] = h->net_u8[1]; h->color_pitch = (size_t)h->w * 3; h->color_frame = nf; }

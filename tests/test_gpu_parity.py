@@ -378,23 +378,33 @@ def test_heatmap_after_reproject_uses_fused_minmax(calibs, demo_pair):
 
 
 # ---- a8: resize path -------------------------------------------------------------------------------------------------
-@pytest.mark.parametrize("src,dst", [((1920, 1080), (640, 480)), ((1280, 960), (640, 480)), ((1242, 375), (640, 192))])
-def test_resize_path(calibs, src, dst):
-    from stereoalgorithms_b200.geometry import DENSE
+@pytest.mark.parametrize("src,dst", [((1920, 1080), (640, 480)), ((1280, 960), (640, 480)), ((1242, 375), (640, 192)), ((1242, 375), (318, 96)),
+                                     ((1918, 1078), (959, 539)), ((4000, 600), (402, 60))])
+@pytest.mark.parametrize("model,dtype", [("FastACVNet_plus", "f32"), ("RAFTStereo", "f16")])
+def test_resize_path(calibs, src, dst, model, dtype):
+    """a8: rectify at full size -> OpenCV's 8-bit INTER_LINEAR downscale (exact 2x: rounded 2x2 mean) -> tensors; output widths
+    that are / are not multiples of 4, pitched rectified rows of odd source widths, a ~10x reduction; both tensor types."""
+    from stereoalgorithms_b200.geometry import DENSE, F16, F32, MODELS
     W, H = src
     s = W / 640
     c = O.scale_calibration(calibs["calib_a"], s, crop_y=(480 * s - H) / 2)
     li, ri = O.synthetic_image(W, H, 50), O.synthetic_image(W, H, 51)
     d = O.synthetic_disparity(dst[0], dst[1], 52)
-    ref = O.run_pair(O.FASTACVNET_PLUS, c, li, ri, d, net_size=dst)
-    with geom(W, H, model="FastACVNet_plus", net_size=dst) as g:
+    mid = MODELS[model]
+    ref = O.run_pair(mid, c, li, ri, -d if model == "RAFTStereo" else d, net_size=dst, dtype=np.float16 if dtype == "f16" else np.float32)
+    with geom(W, H, model=model, net_size=dst, dtype=F16 if dtype == "f16" else F32, max_batch=2) as g:
         g.set_calibration(c)
-        g.rectify_preprocess(li[None], ri[None])
+        g.rectify_preprocess(np.stack([li, ri]), np.stack([ri, li]))
         assert np.array_equal(g.rectified(1, 0)[0], ref["rect_left"])
-        assert np.array_equal(g.net_image(1, 0)[0], ref["net_left"]) and np.array_equal(g.net_image(1, 1)[0], ref["net_right"])
-        assert np.array_equal(g.tensor(1, 0)[0], ref["tensors"][0]) and np.array_equal(g.tensor(1, 1)[0], ref["tensors"][1])
-        g.set_disparity(d[None, None])
-        pts, _ = g.reproject(1, DENSE)
+        nl, nr = g.net_image(2, 0), g.net_image(2, 1)
+        assert np.array_equal(nl[0], ref["net_left"]) and np.array_equal(nr[0], ref["net_right"])
+        tl, tr = g.tensor(2, 0), g.tensor(2, 1)
+        assert np.array_equal(tl[0], ref["tensors"][0]) and np.array_equal(tr[0], ref["tensors"][1])
+        # second frame of the batch (eyes swapped): resized images / tensors must be those of the swapped rectifications
+        (l1, l2), (r1, r2) = O.rectify_maps(c, (W, H))
+        assert np.array_equal(nl[1], O.resize_linear_u8(OC.remap(ri, l1, l2), dst)) and np.array_equal(nr[1], O.resize_linear_u8(OC.remap(li, r1, r2), dst))
+        g.set_disparity(np.stack([-d if model == "RAFTStereo" else d] * 2)[:, None])
+        pts, _ = g.reproject(2, DENSE)
         assert_close_points(pts[0], ref["points"], "resize path")
 
 

@@ -1,5 +1,5 @@
 mkdir -p gpurun_out
-for wl in raft_realtime_640x480_b64_f16 fastacv_640x480_b64_f32 hitnet_640x480_b64_f32 fastacv_kitti_1242x375_b256_f32 stream_1080p_b64_f32 uhd_2160p_b16_f32; do
+for wl in ${WLS:-raft_realtime_640x480_b64_f16 fastacv_640x480_b64_f32 hitnet_640x480_b64_f32 fastacv_kitti_1242x375_b256_f32 stream_1080p_b64_f32 stream_1080p_resize_640x480_b64_f32 uhd_2160p_b16_f32}; do
   python bench.py --steps 50 --warmup 5 --no-cpu-baseline --e2e-steps 5 --workload $wl > gpurun_out/w_$wl.json 2> gpurun_out/w_$wl.err
   python - <<PY
 import json
