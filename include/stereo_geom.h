@@ -225,6 +225,10 @@ SA_API int sa_reproject_compact_noalloc(float* disparity, size_t disparity_frame
 /* Pinned host memory for the buffers above (cudaMallocHost of TRTFastACVNet_plus.cpp:98-99). */
 SA_API int sa_host_alloc(void** p, size_t bytes);
 SA_API int sa_host_free(void* p);
+/* Page-lock a buffer the caller already owns (cudaHostRegister), so that copies into it run at PCIe speed instead of through
+ * the driver's bounce buffer; unregister before the buffer is freed. */
+SA_API int sa_host_register(void* p, size_t bytes);
+SA_API int sa_host_unregister(void* p);
 
 /* Observability (the reference only prints a wall-clock "inference time", TRTFastACVNet_plus.cpp:165-166). */
 SA_API int sa_stage_time(sa_handle* h, int stage, double* total_ms, long* launches); /* needs SA_FLAG_TIMING; synchronises */

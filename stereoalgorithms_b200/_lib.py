@@ -78,6 +78,8 @@ SIGNATURES = {
     "sa_reproject_compact_noalloc": (_i, [_vp, _sz, _vp, _sz, _sz, _vp, _i, _i, _i, _i, _vp, _vp, _vp, C.c_char_p, _sz]),
     "sa_host_alloc": (_i, [C.POINTER(_vp), _sz]),
     "sa_host_free": (_i, [_vp]),
+    "sa_host_register": (_i, [_vp, _sz]),
+    "sa_host_unregister": (_i, [_vp]),
     "sa_stage_time": (_i, [_vp, _i, C.POINTER(C.c_double), C.POINTER(C.c_long)]),
     "sa_reset_timing": (_i, [_vp]),
     "sa_launch_count": (C.c_long, [_vp]),
@@ -89,6 +91,7 @@ SIGNATURES = {
     "sa_ref_Release": (_i, [_vp]),
     "sa_ref_SetEngine": (_i, [_vp, ENGINE_FN, _vp]),
     "sa_ref_SetStubSeed": (_i, [_vp, _u]),
+    "sa_ref_SetHostRegister": (_i, [_vp, _i]),
     "sa_ref_Geometry": (_vp, [_vp]),
     "sa_ref_LastError": (_cp, [_vp]),
     "sa_ref_Heatmap": (_i, [_vp, _vp]),

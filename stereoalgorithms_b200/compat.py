@@ -92,6 +92,10 @@ class _Model:
     def SetStubSeed(self, p, seed: int) -> int:
         return self._l().sa_ref_SetStubSeed(p, int(seed))
 
+    def SetHostRegister(self, p, on: bool) -> int:
+        """Page-locking of a reused pointcloud buffer (sa_ref_SetHostRegister); on by default."""
+        return self._l().sa_ref_SetHostRegister(p, 1 if on else 0)
+
     def Geometry(self, p):
         return self._l().sa_ref_Geometry(p)
 

@@ -885,6 +885,22 @@ int sa_host_alloc(void** p, size_t bytes)
     return SA_OK;
 }
 
+int sa_host_register(void* p, size_t bytes)
+{
+    if (!p || bytes == 0) return SA_ERR_INVALID_ARG;
+    const cudaError_t e = cudaHostRegister(p, bytes, cudaHostRegisterDefault);
+    if (e != cudaSuccess) { cudaGetLastError(); return fail(nullptr, SA_ERR_CUDA, "sa_host_register(%zu): %s", bytes, cudaGetErrorString(e)); }
+    return SA_OK;
+}
+
+int sa_host_unregister(void* p)
+{
+    if (!p) return SA_OK;
+    const cudaError_t e = cudaHostUnregister(p);
+    if (e != cudaSuccess) { cudaGetLastError(); return fail(nullptr, SA_ERR_CUDA, "sa_host_unregister: %s", cudaGetErrorString(e)); }
+    return SA_OK;
+}
+
 int sa_host_free(void* p)
 {
     if (!p) return SA_OK;

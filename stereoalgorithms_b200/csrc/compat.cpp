@@ -23,7 +23,32 @@ struct Algorithm {
     unsigned stub_seed = 1;
     std::string err;
     std::vector<uint8_t> tmp;
+    // page-locking of a point-cloud buffer the caller reuses (sa_ref_SetHostRegister)
+    bool host_register = true;
+    float* pc_seen = nullptr;      // pointer of the previous Run
+    float* pc_reg = nullptr;       // registered pointer ...
+    size_t pc_reg_bytes = 0;       // ... and its size
+    float* pc_failed = nullptr;    // registration of this pointer failed: do not retry on every call
 };
+
+void drop_registration(Algorithm* a)
+{
+    if (a->pc_reg) sa_host_unregister(a->pc_reg);
+    a->pc_reg = nullptr;
+    a->pc_reg_bytes = 0;
+}
+
+void track_pointcloud_buffer(Algorithm* a, float* pointcloud, size_t bytes)
+{
+    if (!a->host_register) return;
+    if (pointcloud == a->pc_reg && bytes <= a->pc_reg_bytes) { a->pc_seen = pointcloud; return; }
+    if (a->pc_reg) drop_registration(a);                             // another buffer (or a larger image): forget the old one
+    if (pointcloud == a->pc_seen && pointcloud != a->pc_failed) {   // second call in a row with this buffer: worth pinning
+        if (sa_host_register(pointcloud, bytes) == SA_OK) { a->pc_reg = pointcloud; a->pc_reg_bytes = bytes; }
+        else a->pc_failed = pointcloud;                              // e.g. the caller registered it already - which is just as good
+    }
+    a->pc_seen = pointcloud;
+}
 
 bool file_exists(const char* p)
 {
@@ -117,6 +142,7 @@ int sa_ref_Run(void* p, int rectify, sa_image* left, sa_image* right, float* poi
         rc = sa_stub_disparity(g, 1, a->stub_seed, nullptr);
         if (rc != SA_OK) { a->err = sa_last_error(g); return -1; }
     }
+    track_pointcloud_buffer(a, pointcloud, (size_t)W * H * 6 * sizeof(float));
     rc = sa_reproject(g, 1, SA_DENSE, pointcloud, nullptr, SA_HOST, nullptr);
     if (rc != SA_OK) { a->err = sa_last_error(g); return -1; }
     if (disparity) {
@@ -155,8 +181,18 @@ int sa_ref_Release(void* p)
 {
     Algorithm* a = static_cast<Algorithm*>(p);
     if (!a) return -1;
+    drop_registration(a);
     if (a->geom) sa_destroy(a->geom);
     delete a;
+    return 0;
+}
+
+int sa_ref_SetHostRegister(void* p, int on)
+{
+    Algorithm* a = static_cast<Algorithm*>(p);
+    if (!a) return -1;
+    a->host_register = on != 0;
+    if (!on) drop_registration(a);
     return 0;
 }
 

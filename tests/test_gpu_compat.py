@@ -55,6 +55,41 @@ def test_demo_main_fastacvnet_plus(demo_pair, calibs, tmp_path):
     assert F.Release(fastacvnet) == 0
 
 
+def test_reused_pointcloud_buffer_is_page_locked_and_results_do_not_change(demo_pair, calibs):
+    """The demos pass the same `pointcloud` to every Run (FastACVNet_plus/test/main.cpp:40-50); from the second call on the
+    library page-locks it.  Results must not depend on that, on switching buffers, or on switching the feature off."""
+    from stereoalgorithms_b200 import _lib as L
+    from stereoalgorithms_b200.compat import FastACVNet_plus as F, Mat
+    lib = L.load()
+    imageL, imageR = demo_pair
+    p = F.Initialize("m.onnx", 0, CALIB)
+    n = imageL.shape[0] * imageL.shape[1] * 6
+    bufs = [np.zeros(n, np.float32), np.zeros(n, np.float32)]
+    d = Mat()
+    outs = []
+    for buf_i in (0, 0, 0, 1, 1, 0, 0):                      # pinned from call 2; dropped and re-pinned as the buffer changes
+        bufs[buf_i][:] = 0
+        assert F.RunFastACVNet_plus_RectifyImage(p, imageL.copy(), imageR.copy(), bufs[buf_i], d) == 0
+        outs.append(bufs[buf_i].copy())
+    for o in outs[1:]:
+        assert np.array_equal(o, outs[0], equal_nan=True)
+    # a buffer the caller page-locked already: registration fails inside, the call still works
+    own = np.zeros(n, np.float32)
+    assert lib.sa_host_register(own.ctypes.data, own.nbytes) == 0
+    for _ in range(3):
+        assert F.RunFastACVNet_plus_RectifyImage(p, imageL.copy(), imageR.copy(), own, d) == 0
+    assert np.array_equal(own, outs[0], equal_nan=True)
+    assert lib.sa_host_unregister(own.ctypes.data) == 0
+    assert F.SetHostRegister(p, False) == 0
+    for _ in range(3):
+        bufs[0][:] = 0
+        assert F.RunFastACVNet_plus_RectifyImage(p, imageL.copy(), imageR.copy(), bufs[0], d) == 0
+    assert np.array_equal(bufs[0], outs[0], equal_nan=True)
+    assert F.Release(p) == 0
+    # released: the buffer is ordinary memory again and can be registered by someone else
+    assert lib.sa_host_register(bufs[0].ctypes.data, bufs[0].nbytes) == 0 and lib.sa_host_unregister(bufs[0].ctypes.data) == 0
+
+
 @pytest.mark.parametrize("name", ["RAFTStereo", "HitNet", "CREStereo"])
 def test_other_models(demo_pair, calibs, name):
     from stereoalgorithms_b200 import compat
