@@ -444,6 +444,35 @@ def test_run_batch_host_to_host(calibs, demo_pair, model):
         assert_close_points(pin[2].array[2], ref_pts, "stub frame 2")
 
 
+@pytest.mark.parametrize("size", [(1242, 375), (322, 241)])
+def test_run_batch_odd_width(calibs, size):
+    """The whole host-to-host flow at a width that is not a multiple of 4: the rectified rows are padded on the device, the
+    caller still gets dense images back; ordinary (pageable) host buffers."""
+    W, H = size
+    s = W / 640
+    c = O.scale_calibration(calibs["calib_a"], s, crop_y=(480 * s - H) / 2)
+    n = 5
+    rng = np.random.default_rng(W)
+    L = rng.integers(0, 256, (n, H, W, 3), dtype=np.uint8)
+    R = rng.integers(0, 256, (n, H, W, 3), dtype=np.uint8)
+    D = np.stack([O.synthetic_disparity(W, H, 300 + i) for i in range(n)])[:, None]
+    pts, disp = np.zeros((n, W * H, 6), np.float32), np.zeros((n, H, W), np.float32)
+    rl, rr, hm = np.zeros_like(L), np.zeros_like(R), np.zeros((n, H, W, 3), np.uint8)
+    with geom(W, H, model="CREStereo", max_batch=8) as g:
+        g.set_calibration(c)
+        g.set_option("chunk", 2)
+        dd = np.zeros((n, 2, H, W), np.float32)
+        dd[:, :1] = D
+        g.set_disparity(dd)
+        g.run_batch(L, R, n, rectify=True, stub_seed=0, pointcloud=pts, disparity=disp, rect_left=rl, rect_right=rr, heatmap=hm)
+        for i in range(n):
+            ref = O.run_pair(O.CRESTEREO, c, L[i], R[i], D[i, 0])
+            assert np.array_equal(rl[i], ref["rect_left"]) and np.array_equal(rr[i], ref["rect_right"]), i
+            assert_close_points(pts[i], ref["points"], f"run_batch odd {i}")
+            assert np.array_equal(disp[i], ref["disparity"]) and np.array_equal(hm[i], ref["heatmap"])
+        assert np.array_equal(g.rectified(n, 1), rr)
+
+
 # ---- errors ----------------------------------------------------------------------------------------------------------
 def test_error_behaviour(demo_pair, tmp_path):
     from stereoalgorithms_b200 import _lib as L
