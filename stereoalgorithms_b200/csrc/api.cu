@@ -229,6 +229,7 @@ static int stage_rectify(sa_handle* h, int f0, int n, const uint8_t* src_l, cons
         p.tensor[0] = t_l; p.tensor[1] = t_r; p.lut = lut;
         p.src_pitch = (size_t)h->w * 3; p.src_frame = nf; p.tensor_frame = tframe;
         p.W = h->w; p.H = h->h; p.n = n; p.model = h->cfg.model; p.dtype = h->cfg.tensor_dtype;
+        p.force_scalar = (int)h->opt_scalar_preprocess;
         StageScope t(h, SA_STAGE_RESIZE, s);
         // (a fused resize + preprocess kernel - 128 x 8 output pixels per CTA, source rows staged with cp.async - was built
         // and measured slower on 64 pairs 1080p -> 640x480: 0.54 vs 0.43 ms for these two launches; it was removed)
@@ -240,6 +241,7 @@ static int stage_rectify(sa_handle* h, int f0, int n, const uint8_t* src_l, cons
         p.src[0] = src_l; p.src[1] = src_r; p.tensor[0] = t_l; p.tensor[1] = t_r; p.lut = lut;
         p.src_pitch = pitch; p.src_frame = frame_bytes; p.tensor_frame = tframe;
         p.W = h->W; p.H = h->H; p.n = n; p.model = h->cfg.model; p.dtype = h->cfg.tensor_dtype;
+        p.force_scalar = (int)h->opt_scalar_preprocess;
         StageScope t(h, SA_STAGE_RECTIFY, s);
         SA_CUDA(h, launch_preprocess(p, s, &h->launches));
     }
@@ -950,6 +952,7 @@ int sa_set_option(sa_handle* h, const char* key, long value)
     else if (!std::strcmp(key, "bulk")) h->opt_bulk = value;
     else if (!std::strcmp(key, "force_unaligned")) h->opt_force_unaligned = value;
     else if (!std::strcmp(key, "no_fixed_size")) h->opt_no_fixed_size = value;
+    else if (!std::strcmp(key, "scalar_preprocess")) h->opt_scalar_preprocess = value;
     else if (!std::strcmp(key, "l2_prefetch")) h->opt_l2_prefetch = value;
     else return fail(h, SA_ERR_INVALID_ARG, "sa_set_option: unknown key '%s'", key);
     return SA_OK;

@@ -106,6 +106,7 @@ struct sa_handle {
     long opt_persistent = 0;          // CTAs per SM of the persistent rectify kernel (0 = one CTA per tile, the default: measured faster)
     long opt_batch_ctas = 0;           // CTAs per SM of the batch kernel; 0 = automatic (launch_rectify_t)
     long opt_force_unaligned = 0;
+    long opt_scalar_preprocess = 0;   // preprocess_kernel (one pixel per thread) instead of preprocess4_kernel
     long opt_no_fixed_size = 0;
     long opt_l2_prefetch = -1;        // see RectifyArgs::l2_prefetch; -1 = automatic
     long opt_bulk = 0;                // rectify_tma_kernel when the frames are 16-byte aligned
@@ -183,6 +184,7 @@ struct PreprocArgs {  // rectify = 0 path, and the second half of the resize pat
     const void* lut;
     size_t src_pitch, src_frame, tensor_frame;
     int W, H, n, model, dtype;
+    int force_scalar;   // 1: one pixel per thread even where the four-pixel kernel applies (tests)
 };
 cudaError_t launch_preprocess(const PreprocArgs& a, cudaStream_t s, long* launches);
 

@@ -910,6 +910,68 @@ __global__ void __launch_bounds__(256) preprocess_kernel(const PreprocArgs a)
     t[0] = r; t[plane] = g; t[2 * plane] = b;
 }
 
+// Same operation, four pixels per thread: for rows that start on 4-byte boundaries and widths that are a multiple of 4 (every
+// 640 / 1280 / 1920-wide input; the resized network images) a thread reads its 12 bytes as three words and writes four
+// consecutive elements of each plane with one 16-byte (f32) or 8-byte (f16) store.  A CTA covers 4096 pixels so that the LUT
+// is staged once per 4096 look-ups; a thread's four groups are 256 groups apart (a warp reads 384 contiguous bytes).
+// Measured on 64 pairs of 640x480 f32: 0.183 ms with one pixel per thread (byte loads, 4-byte stores) -> see DESIGN.md section 5.
+constexpr int kPreGroups = 4;     // 4-pixel groups per thread
+
+template <int DTYPE, bool IDENT>
+__global__ void __launch_bounds__(256) preprocess4_kernel(const PreprocArgs a)
+{
+    using T = typename TensorT<DTYPE>::type;
+    __shared__ T s_lut[IDENT ? 1 : 768];
+    if (!IDENT) {
+        const T* lut = static_cast<const T*>(a.lut);
+        for (int i = threadIdx.x; i < 768; i += 256) s_lut[i] = lut[i];
+    }
+    const int eye = blockIdx.y & 1, frame = blockIdx.y >> 1;
+    const int gw = a.W >> 2;                                       // groups per row
+    const int ngroups = gw * a.H;
+    const uint8_t* src = (eye ? a.src[1] : a.src[0]) + (size_t)frame * a.src_frame;
+    T* tbase = static_cast<T*>(eye ? a.tensor[1] : a.tensor[0]) + (size_t)frame * a.tensor_frame;
+    const size_t plane = (size_t)a.W * a.H;
+    uint32_t u[kPreGroups][3];
+    int gi[kPreGroups];
+#pragma unroll
+    for (int j = 0; j < kPreGroups; j++) {                            // all loads first
+        const int g = (blockIdx.x * kPreGroups + j) * 256 + threadIdx.x;
+        gi[j] = g < ngroups ? g : -1;
+        u[j][0] = u[j][1] = u[j][2] = 0u;
+        if (g < ngroups) {
+            const int y = g / gw, x4 = g - y * gw;
+            const uint32_t* p = reinterpret_cast<const uint32_t*>(src + (size_t)y * a.src_pitch) + 3 * x4;
+            u[j][0] = __ldg(p); u[j][1] = __ldg(p + 1); u[j][2] = __ldg(p + 2);
+        }
+    }
+    if (!IDENT) __syncthreads();
+#pragma unroll
+    for (int j = 0; j < kPreGroups; j++) {
+        if (gi[j] < 0) continue;
+        // bytes: B0 G0 R0 B1 | G1 R1 B2 G2 | R2 B3 G3 R3
+        const uint32_t w0 = u[j][0], w1 = u[j][1], w2 = u[j][2];
+        const uint32_t B[4] = {w0 & 0xffu, w0 >> 24, (w1 >> 16) & 0xffu, (w2 >> 8) & 0xffu};
+        const uint32_t G[4] = {(w0 >> 8) & 0xffu, w1 & 0xffu, w1 >> 24, (w2 >> 16) & 0xffu};
+        const uint32_t Rr[4] = {(w0 >> 16) & 0xffu, (w1 >> 8) & 0xffu, w2 & 0xffu, w2 >> 24};
+        T r[4], g[4], b[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) normalise<DTYPE, IDENT, T>(s_lut, B[k], G[k], Rr[k], r[k], g[k], b[k]);
+        T* t = tbase + (size_t)gi[j] * 4;
+        if (DTYPE == SA_F16) {
+            struct alignas(8) H4 { T v[4]; };
+            *reinterpret_cast<H4*>(t) = H4{{r[0], r[1], r[2], r[3]}};
+            *reinterpret_cast<H4*>(t + plane) = H4{{g[0], g[1], g[2], g[3]}};
+            *reinterpret_cast<H4*>(t + 2 * plane) = H4{{b[0], b[1], b[2], b[3]}};
+        } else {
+            struct alignas(16) F4 { T v[4]; };
+            *reinterpret_cast<F4*>(t) = F4{{r[0], r[1], r[2], r[3]}};
+            *reinterpret_cast<F4*>(t + plane) = F4{{g[0], g[1], g[2], g[3]}};
+            *reinterpret_cast<F4*>(t + 2 * plane) = F4{{b[0], b[1], b[2], b[3]}};
+        }
+    }
+}
+
 inline bool lut_is_identity(int model) { return model == SA_MODEL_RAFTSTEREO || model == SA_MODEL_CRESTEREO; }
 
 template <int DTYPE, bool IDENT, bool WT>
@@ -1003,12 +1065,26 @@ cudaError_t launch_preprocess(const PreprocArgs& a, cudaStream_t s, long* launch
 {
     if (a.n <= 0) return cudaSuccess;
     const size_t plane = (size_t)a.W * a.H;
-    dim3 grid((unsigned)((plane + 255) / 256), 2u * (unsigned)a.n);
     const bool ident = lut_is_identity(a.model);
-    if (a.dtype == SA_F16) {
-        if (ident) preprocess_kernel<SA_F16, true><<<grid, 256, 0, s>>>(a); else preprocess_kernel<SA_F16, false><<<grid, 256, 0, s>>>(a);
+    const size_t telt = a.dtype == SA_F16 ? 2 : 4;
+    // four pixels per thread: word-aligned source rows, W % 4 == 0, and planes / frames of the tensor on 16-byte boundaries
+    const bool vec = !a.force_scalar && a.W % 4 == 0 && ((uintptr_t)a.src[0] | (uintptr_t)a.src[1] | a.src_pitch | a.src_frame) % 4 == 0 &&
+                     ((uintptr_t)a.tensor[0] | (uintptr_t)a.tensor[1] | (a.tensor_frame * telt) | (plane * telt)) % 16 == 0 && plane / 4 < (1u << 30);
+    if (vec) {
+        const unsigned per_cta = 256u * kPreGroups;
+        dim3 grid((unsigned)((plane / 4 + per_cta - 1) / per_cta), 2u * (unsigned)a.n);
+        if (a.dtype == SA_F16) {
+            if (ident) preprocess4_kernel<SA_F16, true><<<grid, 256, 0, s>>>(a); else preprocess4_kernel<SA_F16, false><<<grid, 256, 0, s>>>(a);
+        } else {
+            if (ident) preprocess4_kernel<SA_F32, true><<<grid, 256, 0, s>>>(a); else preprocess4_kernel<SA_F32, false><<<grid, 256, 0, s>>>(a);
+        }
     } else {
-        if (ident) preprocess_kernel<SA_F32, true><<<grid, 256, 0, s>>>(a); else preprocess_kernel<SA_F32, false><<<grid, 256, 0, s>>>(a);
+        dim3 grid((unsigned)((plane + 255) / 256), 2u * (unsigned)a.n);
+        if (a.dtype == SA_F16) {
+            if (ident) preprocess_kernel<SA_F16, true><<<grid, 256, 0, s>>>(a); else preprocess_kernel<SA_F16, false><<<grid, 256, 0, s>>>(a);
+        } else {
+            if (ident) preprocess_kernel<SA_F32, true><<<grid, 256, 0, s>>>(a); else preprocess_kernel<SA_F32, false><<<grid, 256, 0, s>>>(a);
+        }
     }
     if (launches) ++*launches;
     return cudaGetLastError();

@@ -155,15 +155,18 @@ def test_rectified_batch_device_input_and_pitch(calibs, demo_pair):
 # ---- a4 / a10: tensors -----------------------------------------------------------------------------------------
 @pytest.mark.parametrize("model", ["RAFTStereo", "HitNet", "CREStereo", "FastACVNet_plus"])
 @pytest.mark.parametrize("dtype", ["f32", "f16"])
-@pytest.mark.parametrize("rectify", [True, False])
-def test_tensors(calibs, demo_pair, model, dtype, rectify):
+@pytest.mark.parametrize("path", ["rectify", "preprocess4", "preprocess1"])
+def test_tensors(calibs, demo_pair, model, dtype, path):
+    """path: fused rectify + preprocess; rectify = 0 with the four-pixel-per-thread kernel; rectify = 0 with the one-pixel one."""
     from stereoalgorithms_b200.geometry import F16, F32, MODELS
     c = calibs["calib_a"]
     l, r = demo_pair
+    rectify = path == "rectify"
     npdt = np.float16 if dtype == "f16" else np.float32
     rl, rr = O.rectify_pair(c, l, r) if rectify else (l, r)
     want = O.preprocess(MODELS[model], rl, rr, npdt)
     with geom(640, 480, model=model, dtype=F16 if dtype == "f16" else F32, max_batch=2) as g:
+        g.set_option("scalar_preprocess", 1 if path == "preprocess1" else 0)
         g.set_calibration(c)
         g.rectify_preprocess(np.stack([l, l]), np.stack([r, r]), rectify=rectify)
         if model == "HitNet":
@@ -181,6 +184,30 @@ def test_tensors(calibs, demo_pair, model, dtype, rectify):
             else:
                 assert np.all(np.abs(a - b) <= RTOL * np.maximum(np.abs(a), np.abs(b)))   # gate: 1e-5 relative
                 assert np.array_equal(a, b)                       # and in fact identical (LUT built the same way)
+
+
+@pytest.mark.parametrize("size,pitch", [((644, 37), 0), ((640, 33), 1936), ((322, 41), 0), ((64, 3), 0)])
+def test_tensors_without_rectification_odd_shapes(size, pitch):
+    """rectify = 0 on device input: widths / pitches where the four-pixel kernel applies with a partial last CTA (644 = 161
+    groups per row), pitched rows, and shapes that must fall back to the one-pixel kernel (W % 4 != 0)."""
+    import torch
+    W, H = size
+    n = 3
+    rng = np.random.default_rng(W * H)
+    L = rng.integers(0, 256, (n, H, W, 3), dtype=np.uint8)
+    R = rng.integers(0, 256, (n, H, W, 3), dtype=np.uint8)
+    if pitch:
+        Lp, Rp = np.zeros((n, H, pitch), np.uint8), np.zeros((n, H, pitch), np.uint8)
+        Lp[:, :, :3 * W], Rp[:, :, :3 * W] = L.reshape(n, H, -1), R.reshape(n, H, -1)
+        dl, dr = torch.from_numpy(Lp).cuda(), torch.from_numpy(Rp).cuda()
+    else:
+        dl, dr = torch.from_numpy(L).cuda(), torch.from_numpy(R).cuda()
+    with geom(W, H, model="FastACVNet_plus", max_batch=n) as g:
+        g.rectify_preprocess(dl, dr, n=n, pitch=pitch, rectify=False)
+        tl, tr = g.tensor(n, 0), g.tensor(n, 1)
+        for i in range(n):
+            wl, wr = O.preprocess(O.FASTACVNET_PLUS, L[i], R[i], np.float32)
+            assert np.array_equal(tl[i], wl) and np.array_equal(tr[i], wr), (size, i)
 
 
 # ---- a5 / a9: reprojection ---------------------------------------------------------------------------------------
