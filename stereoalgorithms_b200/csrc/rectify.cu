@@ -5,17 +5,27 @@
 // (FastACVNet_plus/src/FastACVNet_plus_preprocess.cu:4-39 and the three siblings).
 //
 // One CTA (256 threads) produces a 64x16 tile of the rectified image:
-//   1. each thread reads the map entries of its 4 pixels (coalesced; maps are batch-shared and L2 resident);
+//   1. each thread reads the per-pixel table entry (footprint offset | fx | fy, derived from the maps per calibration)
+//      of its 4 pixels - once per batch in the default kernel, which keeps them in registers while it walks the frames;
 //   2. the CTA stages the tile's source footprint - a bounding box precomputed per tile at calibration time -
 //      from global memory into shared memory as one BGRx word per pixel, zero outside the image, so that
 //      BORDER_CONSTANT needs no per-tap test afterwards;
 //   3. each thread blends its pixels with OpenCV's exact fixed-point arithmetic
 //         dst = (p00*w00 + p01*w01 + p10*w10 + p11*w11 + 2^14) >> 15,  w = (32-fx|fx)*(32-fy|fy)*32
 //      evaluated as ((top*(32-fy) + bot*fy + 512) >> 10), which is the same integer because nothing is rounded
-//      in between; B and R share one 32-bit multiply (two 16-bit lanes);
+//      in between: the horizontal pass on the byte dot-product unit (IDP.4A), the vertical one as a 16-bit dot product
+//      with the rounding constant as its accumulator (IDP.2A);
 //   4. the normalised RGB planes go straight to global memory (a warp writes 32 consecutive floats/halves of a
 //      plane row); the rectified BGR bytes of four neighbouring lanes are packed into three words with one
-//      shuffle + byte-permute and leave as 96-byte coalesced row segments (edge tiles: through shared memory).
+//      shuffle + byte-permute and leave as 96-byte coalesced row segments (the rectified buffer is internal and its
+//      rows are padded to whole 4-pixel groups, so this works for every width).
+//
+// Kernels in this file (DESIGN.md section 3 has the measurements):
+//   rectify_batch_kernel       default: one CTA per (tile, eye) walks a run of frames; A4 / !A4 / PART / 640x480 instantiations
+//   rectify_tma_kernel         option bulk=1: same decomposition, footprint by cp.async.bulk.tensor + mbarrier ring (slower)
+//   rectify_kernel             one CTA per (tile, frame); batch_loop=0 and the bounds-checked tile_generic path
+//   rectify_persistent_kernel  option persistent>0: software-pipelined over arbitrary tiles (slower)
+//   preprocess4_kernel / preprocess_kernel   rectify = 0 and the tail of the resize path: normalise + planarise only
 #include <cuda.h>   // CUtensorMap and its enums only; the one driver function used is fetched with cudaGetDriverEntryPoint
 
 #include "common.h"
