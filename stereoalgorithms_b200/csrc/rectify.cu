@@ -982,6 +982,78 @@ __global__ void __launch_bounds__(256) preprocess4_kernel(const PreprocArgs a)
     }
 }
 
+// Dense frames of ANY width (1242x375: W % 4 != 0, frames and planes only 2- or 8-byte aligned): with contiguous rows a frame is
+// one linear run of pixels, so a thread again takes four of them - 12 bytes from the enclosing aligned words, funnel-shifted
+// by the address's low bits - and writes four consecutive elements of each plane, in stores as wide as the alignment of the
+// planes allows (SW bytes: 16 / 8 / 4 for f32, 8 / 4 / 2 for f16).  The npix % 4 pixels at the end of a frame are done by
+// the first threads of the last CTA one at a time.
+template <int DTYPE, bool IDENT, int SW>
+__global__ void __launch_bounds__(256) preprocess_lin_kernel(const PreprocArgs a)
+{
+    using T = typename TensorT<DTYPE>::type;
+    __shared__ T s_lut[IDENT ? 1 : 768];
+    if (!IDENT) {
+        const T* lut = static_cast<const T*>(a.lut);
+        for (int i = threadIdx.x; i < 768; i += 256) s_lut[i] = lut[i];
+    }
+    const int eye = blockIdx.y & 1, frame = blockIdx.y >> 1;
+    const size_t plane = (size_t)a.W * a.H;
+    const int ngroups = (int)(plane >> 2);
+    const uint8_t* src = (eye ? a.src[1] : a.src[0]) + (size_t)frame * a.src_frame;
+    T* tbase = static_cast<T*>(eye ? a.tensor[1] : a.tensor[0]) + (size_t)frame * a.tensor_frame;
+    uint32_t u[kPreGroups][4];
+    uint32_t sh[kPreGroups];
+    int gi[kPreGroups];
+#pragma unroll
+    for (int j = 0; j < kPreGroups; j++) {                            // all loads first
+        const int g = (blockIdx.x * kPreGroups + j) * 256 + threadIdx.x;
+        gi[j] = g < ngroups ? g : -1;
+        u[j][0] = u[j][1] = u[j][2] = u[j][3] = 0u;
+        sh[j] = 0u;
+        if (g < ngroups) {
+            const uintptr_t A = reinterpret_cast<uintptr_t>(src + (size_t)g * 12);
+            const uint32_t al = (uint32_t)A & 3u;
+            const uint32_t* p = reinterpret_cast<const uint32_t*>(A - al);
+            u[j][0] = __ldg(p); u[j][1] = __ldg(p + 1); u[j][2] = __ldg(p + 2);
+            if (al) u[j][3] = __ldg(p + 3);                           // holds bytes of the group whenever it is needed: never past the data
+            sh[j] = al << 3;
+        }
+    }
+    if (!IDENT) __syncthreads();
+#pragma unroll
+    for (int j = 0; j < kPreGroups; j++) {
+        if (gi[j] < 0) continue;
+        const uint32_t w0 = __funnelshift_r(u[j][0], u[j][1], sh[j]), w1 = __funnelshift_r(u[j][1], u[j][2], sh[j]), w2 = __funnelshift_r(u[j][2], u[j][3], sh[j]);
+        const uint32_t B[4] = {w0 & 0xffu, w0 >> 24, (w1 >> 16) & 0xffu, (w2 >> 8) & 0xffu};
+        const uint32_t G[4] = {(w0 >> 8) & 0xffu, w1 & 0xffu, w1 >> 24, (w2 >> 16) & 0xffu};
+        const uint32_t Rr[4] = {(w0 >> 16) & 0xffu, (w1 >> 8) & 0xffu, w2 & 0xffu, w2 >> 24};
+        T v[3][4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) normalise<DTYPE, IDENT, T>(s_lut, B[k], G[k], Rr[k], v[0][k], v[1][k], v[2][k]);
+        T* t = tbase + (size_t)gi[j] * 4;
+        constexpr int per = SW / (int)sizeof(T);                      // elements per store: 4, 2 or 1
+#pragma unroll
+        for (int c = 0; c < 3; c++) {
+            T* q = t + (size_t)c * plane;
+            if (per == 4) { struct alignas(SW) V { T e[4]; }; *reinterpret_cast<V*>(q) = V{{v[c][0], v[c][1], v[c][2], v[c][3]}}; }
+            else if (per == 2) {
+                struct alignas(SW) V { T e[2]; };
+                *reinterpret_cast<V*>(q) = V{{v[c][0], v[c][1]}};
+                *reinterpret_cast<V*>(q + 2) = V{{v[c][2], v[c][3]}};
+            } else { q[0] = v[c][0]; q[1] = v[c][1]; q[2] = v[c][2]; q[3] = v[c][3]; }
+        }
+    }
+    // the last npix % 4 pixels of the frame
+    const int tail = (int)(plane & 3);
+    if (blockIdx.x == gridDim.x - 1 && (int)threadIdx.x < tail) {
+        const size_t p = (plane & ~(size_t)3) + threadIdx.x;
+        const uint8_t* q = src + p * 3;
+        T r, g, b;
+        normalise<DTYPE, IDENT, T>(s_lut, q[0], q[1], q[2], r, g, b);
+        tbase[p] = r; tbase[plane + p] = g; tbase[2 * plane + p] = b;
+    }
+}
+
 inline bool lut_is_identity(int model) { return model == SA_MODEL_RAFTSTEREO || model == SA_MODEL_CRESTEREO; }
 
 template <int DTYPE, bool IDENT, bool WT>
@@ -1088,6 +1160,17 @@ cudaError_t launch_preprocess(const PreprocArgs& a, cudaStream_t s, long* launch
         } else {
             if (ident) preprocess4_kernel<SA_F32, true><<<grid, 256, 0, s>>>(a); else preprocess4_kernel<SA_F32, false><<<grid, 256, 0, s>>>(a);
         }
+    } else if (!a.force_scalar && a.src_pitch == (size_t)a.W * 3 && plane >= 4 && plane / 4 < (1u << 30) &&
+               ((uintptr_t)a.tensor[0] | (uintptr_t)a.tensor[1]) % 16 == 0) {
+        // dense frames of any width: linear four-pixel kernel, stores as wide as the planes' alignment allows
+        const size_t al = (a.tensor_frame * telt) | (plane * telt);
+        const int sw = al % 16 == 0 ? 16 : (al % 8 == 0 ? 8 : (al % 4 == 0 ? 4 : 2));
+        const unsigned per_cta = 256u * kPreGroups;
+        dim3 grid((unsigned)((plane / 4 + per_cta - 1) / per_cta), 2u * (unsigned)a.n);
+#define SA_LIN(DT, SWB) do { if (ident) preprocess_lin_kernel<DT, true, SWB><<<grid, 256, 0, s>>>(a); else preprocess_lin_kernel<DT, false, SWB><<<grid, 256, 0, s>>>(a); } while (0)
+        if (a.dtype == SA_F16) { if (sw >= 8) SA_LIN(SA_F16, 8); else if (sw == 4) SA_LIN(SA_F16, 4); else SA_LIN(SA_F16, 2); }
+        else { if (sw == 16) SA_LIN(SA_F32, 16); else if (sw == 8) SA_LIN(SA_F32, 8); else SA_LIN(SA_F32, 4); }
+#undef SA_LIN
     } else {
         dim3 grid((unsigned)((plane + 255) / 256), 2u * (unsigned)a.n);
         if (a.dtype == SA_F16) {

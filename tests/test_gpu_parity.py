@@ -186,11 +186,15 @@ def test_tensors(calibs, demo_pair, model, dtype, path):
                 assert np.array_equal(a, b)                       # and in fact identical (LUT built the same way)
 
 
-@pytest.mark.parametrize("size,pitch", [((644, 37), 0), ((640, 33), 1936), ((322, 41), 0), ((64, 3), 0)])
-def test_tensors_without_rectification_odd_shapes(size, pitch):
-    """rectify = 0 on device input: widths / pitches where the four-pixel kernel applies with a partial last CTA (644 = 161
-    groups per row), pitched rows, and shapes that must fall back to the one-pixel kernel (W % 4 != 0)."""
+@pytest.mark.parametrize("size,pitch", [((644, 37), 0), ((640, 33), 1936), ((322, 41), 0), ((64, 3), 0), ((333, 77), 0), ((1242, 375), 0),
+                                        ((321, 5), 970), ((3, 1), 0)])
+@pytest.mark.parametrize("model,dtype", [("FastACVNet_plus", "f32"), ("HitNet", "f16"), ("RAFTStereo", "f16"), ("CREStereo", "f32")])
+def test_tensors_without_rectification_odd_shapes(size, pitch, model, dtype):
+    """rectify = 0 on device input.  Three kernels share this path: four pixels per thread for word-aligned rows of W % 4 = 0
+    (644 = 161 groups per row: partial last CTA; pitched rows), the linear four-pixel kernel for dense frames of any width
+    (planes aligned to 8, 4 or 2 bytes only; npix % 4 tail pixels), one pixel per thread for the rest (odd width AND pitch)."""
     import torch
+    from stereoalgorithms_b200.geometry import F16, F32, MODELS
     W, H = size
     n = 3
     rng = np.random.default_rng(W * H)
@@ -202,12 +206,17 @@ def test_tensors_without_rectification_odd_shapes(size, pitch):
         dl, dr = torch.from_numpy(Lp).cuda(), torch.from_numpy(Rp).cuda()
     else:
         dl, dr = torch.from_numpy(L).cuda(), torch.from_numpy(R).cuda()
-    with geom(W, H, model="FastACVNet_plus", max_batch=n) as g:
+    npdt = np.float16 if dtype == "f16" else np.float32
+    with geom(W, H, model=model, dtype=F16 if dtype == "f16" else F32, max_batch=n) as g:
         g.rectify_preprocess(dl, dr, n=n, pitch=pitch, rectify=False)
-        tl, tr = g.tensor(n, 0), g.tensor(n, 1)
+        tl = g.tensor(n, 0)
+        tr = None if model == "HitNet" else g.tensor(n, 1)
         for i in range(n):
-            wl, wr = O.preprocess(O.FASTACVNET_PLUS, L[i], R[i], np.float32)
-            assert np.array_equal(tl[i], wl) and np.array_equal(tr[i], wr), (size, i)
+            want = O.preprocess(MODELS[model], L[i], R[i], npdt)
+            if model == "HitNet":
+                assert np.array_equal(tl[i], want), (size, i)
+            else:
+                assert np.array_equal(tl[i], want[0]) and np.array_equal(tr[i], want[1]), (size, i)
 
 
 # ---- a5 / a9: reprojection ---------------------------------------------------------------------------------------
