@@ -65,6 +65,8 @@ SA_API int sa_write_pointcloud_txt(const char* path, const float* points, size_t
  * binary little-endian (binary != 0, 15 bytes per point) or ASCII.  skip_non_finite != 0 drops points whose x, y or z is
  * inf/NaN (the dense cloud has them wherever the disparity is 0). */
 SA_API int sa_write_pointcloud_ply(const char* path, const float* points, size_t n_points, int binary, int skip_non_finite);
+/* ... and as a PCD v0.7 file (Point Cloud Library): FIELDS x y z rgb, rgb packed 0x00RRGGBB in a 32-bit unsigned, DATA binary. */
+SA_API int sa_write_pointcloud_pcd(const char* path, const float* points, size_t n_points, int skip_non_finite);
 /* Lossless stand-ins for the demos' cv::imwrite calls (FastACVNet_plus/test/main.cpp:55,59; no JPEG codec here):
  * binary Netpbm.  sa_write_pgm: 8-bit grey (P5), e.g. the output of sa_disparity_u8.  sa_write_ppm_bgr: a BGR image
  * as OpenCV holds it (rectified frame, heat map) written as RGB (P6).  step = bytes per row, 0 = packed. */

@@ -97,6 +97,7 @@ SIGNATURES = {
     "sa_ref_Heatmap": (_i, [_vp, _vp]),
     "sa_write_pointcloud_txt": (_i, [_cp, _vp, _sz]),
     "sa_write_pointcloud_ply": (_i, [_cp, _vp, _sz, _i, _i]),
+    "sa_write_pointcloud_pcd": (_i, [_cp, _vp, _sz, _i]),
     "sa_write_pgm": (_i, [_cp, _vp, _i, _i, _sz]),
     "sa_write_ppm_bgr": (_i, [_cp, _vp, _i, _i, _sz]),
 }

@@ -133,6 +133,14 @@ def write_pointcloud_ply(path: str, pointcloud: np.ndarray, binary: bool = True,
         raise OSError(f"sa_write_pointcloud_ply({path}) failed with {rc}")
 
 
+def write_pointcloud_pcd(path: str, pointcloud: np.ndarray, skip_non_finite: bool = True) -> None:
+    """x y z r g b points as a binary PCD v0.7 file (FIELDS x y z rgb)."""
+    pts = np.ascontiguousarray(pointcloud, np.float32).reshape(-1, 6)
+    rc = L.load().sa_write_pointcloud_pcd(path.encode(), pts.ctypes.data, pts.shape[0], 1 if skip_non_finite else 0)
+    if rc != 0:
+        raise OSError(f"sa_write_pointcloud_pcd({path}) failed with {rc}")
+
+
 def write_pgm(path: str, grey: np.ndarray) -> None:
     """8-bit grey image as binary PGM - lossless stand-in for cv::imwrite("disparity.jpg", ...) of the demos."""
     g = np.ascontiguousarray(grey, np.uint8)

@@ -263,6 +263,29 @@ int sa_write_pointcloud_ply(const char* path, const float* points, size_t n_poin
     return std::fclose(f) == 0 ? SA_OK : SA_ERR_IO;
 }
 
+int sa_write_pointcloud_pcd(const char* path, const float* points, size_t n_points, int skip_non_finite)
+{
+    if (!path || !points) return SA_ERR_INVALID_ARG;
+    auto finite = [](float v) { return v == v && v - v == 0.0f; };
+    size_t kept = n_points;
+    if (skip_non_finite) {
+        kept = 0;
+        for (size_t i = 0; i < n_points; i++) kept += finite(points[i * 6]) && finite(points[i * 6 + 1]) && finite(points[i * 6 + 2]);
+    }
+    FILE* f = std::fopen(path, "wb");
+    if (!f) return SA_ERR_IO;
+    std::fprintf(f, "# .PCD v0.7 - Point Cloud Data file format\nVERSION 0.7\nFIELDS x y z rgb\nSIZE 4 4 4 4\nTYPE F F F U\nCOUNT 1 1 1 1\n"
+                    "WIDTH %zu\nHEIGHT 1\nVIEWPOINT 0 0 0 1 0 0 0\nPOINTS %zu\nDATA binary\n", kept, kept);
+    bool ok = true;
+    for (size_t i = 0; i < n_points && ok; i++) {
+        const float* q = points + i * 6;
+        if (skip_non_finite && !(finite(q[0]) && finite(q[1]) && finite(q[2]))) continue;
+        const uint32_t rgb = ((uint32_t)(unsigned char)q[3] << 16) | ((uint32_t)(unsigned char)q[4] << 8) | (uint32_t)(unsigned char)q[5];
+        ok = std::fwrite(q, sizeof(float), 3, f) == 3 && std::fwrite(&rgb, 4, 1, f) == 1;
+    }
+    return (std::fclose(f) == 0 && ok) ? SA_OK : SA_ERR_IO;
+}
+
 int sa_write_pgm(const char* path, const uint8_t* grey, int w, int h, size_t step)
 {
     if (!path || !grey || w <= 0 || h <= 0 || (step != 0 && step < (size_t)w)) return SA_ERR_INVALID_ARG;

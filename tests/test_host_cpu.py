@@ -169,6 +169,21 @@ def test_pointcloud_ply_writer(lib, tmp_path):
     assert len(lines) == 4 and lines[0] == "1.5 -0.25 2 255 0 12" and lines[3] == "3 4 5 7 8 9"
 
 
+def test_pointcloud_pcd_writer(lib, tmp_path):
+    pts = np.array([[1.5, -0.25, 2.0, 255, 0, 12], [np.inf, 1, 1, 1, 2, 3], [0.5, 0.25, np.nan, 9, 9, 9], [3, 4, 5, 7, 8, 9]], np.float32)
+    p = str(tmp_path / "cloud.pcd")
+    assert lib.sa_write_pointcloud_pcd(p.encode(), pts.ctypes.data, len(pts), 1) == 0
+    raw = open(p, "rb").read()
+    head, body = raw.split(b"DATA binary\n", 1)
+    assert b"VERSION 0.7" in head and b"FIELDS x y z rgb" in head and b"TYPE F F F U" in head and b"WIDTH 2\n" in head and b"POINTS 2\n" in head
+    rec = np.frombuffer(body, dtype=np.dtype([("xyz", "<f4", 3), ("rgb", "<u4")]))
+    assert len(rec) == 2 and np.array_equal(rec["xyz"], pts[[0, 3], :3])
+    assert rec["rgb"].tolist() == [(255 << 16) | 12, (7 << 16) | (8 << 8) | 9]
+    assert lib.sa_write_pointcloud_pcd(p.encode(), pts.ctypes.data, len(pts), 0) == 0
+    assert b"POINTS 4\n" in open(p, "rb").read()
+    assert lib.sa_write_pointcloud_pcd(None, pts.ctypes.data, 4, 0) < 0
+
+
 def _lib_stereo_rectify(lib, c, size, new_size, flags, alpha):
     a = lambda x: np.ascontiguousarray(np.asarray(x, np.float64).ravel())
     K1, D1, K2, D2, R, T = (a(c[k]) for k in ("intrinsic_left", "distCoeffs_left", "intrinsic_right", "distCoeffs_right", "R", "T"))
