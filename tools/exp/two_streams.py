@@ -1,7 +1,7 @@
 """Experiment: stage A of one half-batch concurrent with stage B of the other (two handles, two streams) vs one 64-pair batch."""
 import sys, time
 import numpy as np, torch
-sys.path.insert(0, ".")
+sys.path.insert(0, ".")  # run from the repo root
 from oracle import oracle as O
 from stereoalgorithms_b200.geometry import StereoGeometry, DENSE, F16
 
