@@ -197,6 +197,7 @@ static int stage_rectify(sa_handle* h, int f0, int n, const uint8_t* src_l, cons
         a.batch_ctas_per_sm = (int)h->opt_batch_ctas;
         a.bulk_copy = (int)h->opt_bulk;
         a.l2_prefetch = (int)h->opt_l2_prefetch;
+        a.chunk_taper = (int)h->opt_chunk_taper;
         a.force_unaligned = (int)h->opt_force_unaligned;
         a.no_fixed_size = (int)h->opt_no_fixed_size;
         a.box_w = h->box_w; a.box_h = h->box_h;
@@ -954,6 +955,7 @@ int sa_set_option(sa_handle* h, const char* key, long value)
     else if (!std::strcmp(key, "no_fixed_size")) h->opt_no_fixed_size = value;
     else if (!std::strcmp(key, "scalar_preprocess")) h->opt_scalar_preprocess = value;
     else if (!std::strcmp(key, "l2_prefetch")) h->opt_l2_prefetch = value;
+    else if (!std::strcmp(key, "chunk_taper")) h->opt_chunk_taper = value < 0 ? 0 : (value > 95 ? 95 : value);
     else return fail(h, SA_ERR_INVALID_ARG, "sa_set_option: unknown key '%s'", key);
     return SA_OK;
 }

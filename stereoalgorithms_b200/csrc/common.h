@@ -108,6 +108,7 @@ struct sa_handle {
     long opt_force_unaligned = 0;
     long opt_scalar_preprocess = 0;   // preprocess_kernel (one pixel per thread) instead of preprocess4_kernel
     long opt_no_fixed_size = 0;
+    long opt_chunk_taper = 50;        // see RectifyArgs::chunk_taper (measured: 1-2 % on the 640x480 and 1242x375 workloads, neutral at 1080p)
     long opt_l2_prefetch = -1;        // see RectifyArgs::l2_prefetch; -1 = automatic
     long opt_bulk = 0;                // rectify_tma_kernel when the frames are 16-byte aligned
     long opt_batch_loop = 1;          // rectify_batch_kernel (default); 0 = one CTA per (tile, eye, frame)
@@ -150,6 +151,8 @@ cudaError_t launch_init_maps(const MapParams& p, int W, int H, int* map1, uint16
 cudaError_t launch_tile_info(const int* map1, const uint16_t* map2, int W, int H, TileInfo* tiles, uint32_t* tmap, int* fp_max, int tiles_x, int tiles_y,
                              int force_direct, cudaStream_t s);
 
+constexpr int kMaxChunks = 32;
+
 struct RectifyArgs {
     const uint8_t* src[2];
     uint8_t* rect[2];
@@ -170,6 +173,9 @@ struct RectifyArgs {
     int batch_loop;                    // > 0 (= SM count): one CTA per (tile, eye) walks a run of frames (rectify_batch_kernel)
     int bulk_copy;                     // 1: stage the footprints with TMA tensor copies + mbarriers (rectify_tma_kernel) when alignment allows
     int no_fixed_size;                 // batch kernel: do not use the 640x480 instantiation (tests, tuning)
+    int chunk_taper;                   // batch kernel: percent by which the first / last frame chunk is longer / shorter than the average (0 = equal chunks)
+    int chunk_tab;                     // 1: chunk c covers frames [chunk_begin[c], chunk_begin[c + 1]) (filled in by launch_rectify_t)
+    int chunk_begin[kMaxChunks + 1];
     size_t rect_pitch, rect_frame;     // bytes per row / per frame of the rectified output (rows padded, see sa_handle::rect_pitch)
     int force_unaligned;               // batch kernel: take the 2-byte-aligned code path even for 4-byte aligned frames (tests, tuning)
     int l2_prefetch;                   // batch kernel: prefetch.global.L2 of the frame this many iterations ahead (0 = off, < 0 = automatic)

@@ -493,8 +493,9 @@ __device__ __forceinline__ void rectify_batch_body(const RectifyArgs& a, int til
     const int tid = threadIdx.x;
     const int W = FW ? FW : a.W, H = FH ? FH : a.H;
     const int eye = blockIdx.z & 1, chunk = blockIdx.z >> 1;
-    const int f0 = chunk * frames_per_cta;
-    int f1 = min(a.n, f0 + frames_per_cta);
+    // equal chunks of frames_per_cta frames, or (chunk_taper) the tapered schedule of launch_rectify_t
+    const int f0 = a.chunk_tab ? a.chunk_begin[chunk] : chunk * frames_per_cta;
+    int f1 = a.chunk_tab ? a.chunk_begin[chunk + 1] : min(a.n, f0 + frames_per_cta);
     const int tx0 = blockIdx.x * kTileW, ty0 = blockIdx.y * kTileH;
     const TileInfo ti = a.tiles[eye][blockIdx.y * tiles_x + blockIdx.x];
     const bool fast = ti.w > 0;                                        // partial tiles at the right/bottom edge stay on this path, with their
@@ -1077,6 +1078,26 @@ cudaError_t launch_rectify_t(const RectifyArgs& a, bool aligned4, int tiles_x, i
         }
         if (fpc > a.n) fpc = a.n;
         const int chunks = (a.n + fpc - 1) / fpc;
+        // Tapered chunks: CTAs are dispatched in grid order (chunk index slowest), so the chunks that start last are made the
+        // shortest - the launch then ends with many short CTAs instead of a few long ones.  Chunk c of C gets
+        // avg * (1 + t * (1 - 2c/(C-1))) frames (t = chunk_taper / 100; the sizes still sum to n).
+        RectifyArgs at = a;
+        at.chunk_tab = 0;
+        if (a.chunk_taper > 0 && chunks >= 2 && chunks <= kMaxChunks) {
+            const double t = a.chunk_taper / 100.0, avg = (double)a.n / chunks;
+            double acc = 0.0;
+            int pos = 0;
+            for (int c = 0; c < chunks; c++) {
+                at.chunk_begin[c] = pos;
+                acc += avg * (1.0 + t * (1.0 - 2.0 * c / (chunks - 1)));
+                int next = (int)(acc + 0.5);
+                if (next <= pos) next = pos + 1;                       // every chunk has at least one frame ...
+                if (next > a.n - (chunks - 1 - c)) next = a.n - (chunks - 1 - c);   // ... and leaves one for each chunk after it
+                pos = next;
+            }
+            at.chunk_begin[chunks] = a.n;
+            at.chunk_tab = 1;
+        }
         if (2 * chunks <= 65535) {
             const dim3 g((unsigned)tiles_x, (unsigned)tiles_y, 2u * (unsigned)chunks);
             // TMA staging: box = largest footprint of the calibration + up to 12 pixels of origin alignment, rows padded to 16 bytes
@@ -1092,9 +1113,9 @@ cudaError_t launch_rectify_t(const RectifyArgs& a, bool aligned4, int tiles_x, i
                     return cudaGetLastError();
                 }
             }
-            if (a4 && a.W == 640 && a.H == 480 && !a.no_fixed_size) rectify_batch_kernel<DTYPE, IDENT, WT, true, 640, 480><<<g, kRectThreads, 0, s>>>(a, tiles_x, out_align, fpc);
-            else if (a4) rectify_batch_kernel<DTYPE, IDENT, WT, true><<<g, kRectThreads, 0, s>>>(a, tiles_x, out_align, fpc);
-            else rectify_batch_kernel<DTYPE, IDENT, WT, false><<<g, kRectThreads, 0, s>>>(a, tiles_x, out_align, fpc);
+            if (a4 && a.W == 640 && a.H == 480 && !a.no_fixed_size) rectify_batch_kernel<DTYPE, IDENT, WT, true, 640, 480><<<g, kRectThreads, 0, s>>>(at, tiles_x, out_align, fpc);
+            else if (a4) rectify_batch_kernel<DTYPE, IDENT, WT, true><<<g, kRectThreads, 0, s>>>(at, tiles_x, out_align, fpc);
+            else rectify_batch_kernel<DTYPE, IDENT, WT, false><<<g, kRectThreads, 0, s>>>(at, tiles_x, out_align, fpc);
             return cudaGetLastError();
         }
     }

@@ -609,6 +609,29 @@ def test_rectified_unaligned_widths_batches(calibs, size, l2_prefetch):
         assert np.array_equal(t, want)
 
 
+@pytest.mark.parametrize("taper", [50, 95])
+@pytest.mark.parametrize("size,ctas", [((640, 480), 4), ((640, 480), 0), ((1242, 375), 8)])
+def test_rectified_tapered_chunks(calibs, size, ctas, taper):
+    """chunk_taper: frame chunks of unequal length (long ones launched first); every frame must still be produced exactly once."""
+    W, H = size
+    s = W / 640
+    c = O.scale_calibration(calibs["calib_a"], s, crop_y=(480 * s - H) / 2) if size != (640, 480) else calibs["calib_a"]
+    n = 41
+    rng = np.random.default_rng(taper + W)
+    base = rng.integers(0, 256, (H, W, 3), dtype=np.uint8)
+    L = np.stack([np.roll(base, 5 * i, axis=1) for i in range(n)])
+    (l1, l2), (r1, r2) = O.rectify_maps(c, (W, H))
+    with geom(W, H, model="RAFTStereo", max_batch=n) as g:
+        g.set_option("batch_ctas", ctas)
+        g.set_option("chunk_taper", taper)
+        g.set_calibration(c)
+        g.rectify_preprocess(L, L)
+        gl, gr = g.rectified(n, 0), g.rectified(n, 1)
+        for i in range(n):
+            assert np.array_equal(gl[i], OC.remap(L[i], l1, l2)), i
+            assert np.array_equal(gr[i], OC.remap(L[i], r1, r2)), i
+
+
 @pytest.mark.parametrize("ctas_per_sm", [1, 16, 1000])
 @pytest.mark.parametrize("bulk", [1, 0, -1])
 def test_rectified_long_batches_all_chunkings(calibs, demo_pair, ctas_per_sm, bulk):
