@@ -44,15 +44,19 @@ SA_API const char* sa_ref_Version(void* p);
 /* Release (:186-190). */
 SA_API int sa_ref_Release(void* p);
 
-/* The network slot: a callback with the device tensors, or (default) the synthetic stub with this seed;
+/* The network slot: a callback with the device tensors and the handle's stream (sa_engine_fn in stereo_geom.h: the stream is
+ * the one both halves run on, never NULL - enqueue on it, do not synchronise), or (default) the synthetic stub with this seed;
  * seed 0 = leave the disparity buffer as the caller prepared it through sa_ref_Geometry + sa_set_disparity. */
 SA_API int sa_ref_SetEngine(void* p, sa_engine_fn fn, void* user);
 SA_API int sa_ref_SetStubSeed(void* p, unsigned seed);
 /* Not in the reference.  The demos allocate `pointcloud` once and pass it to every Run (FastACVNet_plus/test/main.cpp:40-50).
- * When sa_ref_Run sees the same pointcloud pointer on two consecutive calls it page-locks that buffer (sa_host_register), which
- * takes the 7.4 MB device-to-host copy of a 640x480 cloud from ~0.6 ms (pageable) to ~0.15 ms; the registration is dropped when
- * another pointer shows up and in sa_ref_Release - so Release before freeing the buffer, as the demos do.  on = 0 switches
- * this off (default on). */
+ * With on = 1, when sa_ref_Run sees the same pointcloud pointer on two consecutive calls it page-locks that buffer
+ * (sa_host_register), which takes the 7.4 MB device-to-host copy of a 640x480 cloud from ~0.6 ms (pageable) to ~0.15 ms.  The
+ * registration is dropped when another pointer shows up, when this is switched off, and in sa_ref_Release.
+ * OFF by default, because it puts an obligation on the caller the reference does not have: a page-locked buffer must not be
+ * freed behind the library's back (free it after Release, after SetHostRegister(p, 0), or after a Run with another buffer) -
+ * otherwise a later allocation that lands at the same address would be treated as still page-locked and the copy would go to
+ * the old pages. */
 SA_API int sa_ref_SetHostRegister(void* p, int on);
 /* The underlying geometry handle (created lazily for the first image size seen; 640x480 after Initialize). */
 SA_API sa_handle* sa_ref_Geometry(void* p);

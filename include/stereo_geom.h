@@ -152,16 +152,46 @@ SA_API int sa_copy_net_image(sa_handle* h, int n, int eye, uint8_t* out, int whe
 SA_API int sa_copy_tensor(sa_handle* h, int n, int eye, void* out, int where, sa_stream stream);
 SA_API int sa_copy_disparity(sa_handle* h, int n, float* out, int where, sa_stream stream); /* plane 0 -> [n][h][w] */
 SA_API int sa_synchronize(sa_handle* h);
+/* All read-backs of one Run in one call: the two cudaMemcpy D2H of TRTFastACVNet_plus.cpp:163-164 plus the rectified images
+ * the reference leaves in the caller's cv::Mat (FastACVNet_plus_Algorithm.cpp:142-143).  Every requested copy is queued on
+ * one stream and the call synchronises ONCE at the end.  HOST destinations; any of them may be NULL.  pointcloud: the dense
+ * cloud of the last sa_reproject that kept its result in the internal buffer (out = NULL); disparity: plane 0, [n][h][w];
+ * rect_*: rows `*_pitch` bytes apart (0 = 3*W, e.g. cv::Mat::step); heatmap: the result of the last sa_heatmap with out = NULL. */
+SA_API int sa_download(sa_handle* h, int n, float* pointcloud, float* disparity, uint8_t* rect_left, size_t rect_left_pitch, uint8_t* rect_right,
+                       size_t rect_right_pitch, uint8_t* heatmap, sa_stream stream);
+/* The handle's own compute stream (a cudaStream_t; the reference creates one per object with cudaStreamCreate,
+ * TRTFastACVNet_plus.cpp:91).  It is what every call uses when its `stream` argument is NULL, and it is created
+ * cudaStreamNonBlocking: work a caller queues on the legacy default stream is NOT ordered against it.  Never NULL for a
+ * live handle. */
+SA_API sa_stream sa_get_stream(sa_handle* h);
 
 /* The reference's whole Run<Model>[_RectifyImage] data flow for n pairs with HOST buffers (TRTFastACVNet_plus.cpp:
  * 119-170): upload, stage A, network slot, stage B, download - pipelined in chunks over copy/compute streams.
  * Any output pointer may be NULL to skip that download.  The network slot runs the engine callback if one is set,
  * else the synthetic stub when stub_seed != 0, else uses the disparity buffer as it is. */
+/* The callback replaces context->enqueueV3(stream) (TRTFastACVNet_plus.cpp:152).  `stream` is the stream stage A was queued on
+ * and stage B will be queued on - always a real stream, never NULL: enqueue the network on it (or make it wait for an event
+ * of your own stream and signal back) and return without synchronising.  Return 0 on success. */
 typedef int (*sa_engine_fn)(void* user, sa_stream stream, int first_frame, int n, const void* left_tensor,
                             const void* right_tensor, float* disparity);
 SA_API int sa_set_engine(sa_handle* h, sa_engine_fn fn, void* user);
 SA_API int sa_run_batch(sa_handle* h, int n, const uint8_t* left, const uint8_t* right, int rectify, unsigned stub_seed,
                         float* pointcloud, float* disparity, uint8_t* rect_left, uint8_t* rect_right, uint8_t* heatmap);
+
+/* One host batch over several GPUs from one process.  The reference has no multi-GPU path (one object, one device:
+ * cudaSetDevice in Initialize only, TRTFastACVNet_plus.cpp:45); frames share nothing, so the batch is cut frame-wise:
+ * handle g (created on GPU g with max_batch >= ceil(n / n_handles), same sizes / model / tensor type as handle 0, same
+ * calibration loaded) gets the contiguous block sa_shard_range(n, g, n_handles) of the n pairs and runs sa_run_batch on it,
+ * on its own host thread, reading and writing its slice of the caller's HOST buffers (layouts and NULL rules as for
+ * sa_run_batch; use pinned memory - sa_host_alloc - so that the copies of all GPUs really overlap).  Returns when every
+ * shard is home; on failure the status of the first failing shard, its index in *failed_handle (may be NULL) and its
+ * message in sa_last_error(handles[*failed_handle]).  No collective, no peer traffic.  The synthetic stub numbers frames
+ * across shards, so the result equals sa_run_batch of the whole batch on one handle bit for bit. */
+SA_API int sa_run_batch_multi(sa_handle* const* handles, int n_handles, int n, const uint8_t* left, const uint8_t* right, int rectify, unsigned stub_seed,
+                              float* pointcloud, float* disparity, uint8_t* rect_left, uint8_t* rect_right, uint8_t* heatmap, int* failed_handle);
+/* The partition sa_run_batch_multi uses (and bench.py's ranks, stereoalgorithms_b200/sharding.py): blocks of
+ * ceil(n_total / world) pairs, the last ones shorter or empty.  Host only. */
+SA_API int sa_shard_range(int n_total, int rank, int world, int* begin, int* end);
 
 /* Host-only helpers: usable without a CUDA device.
  * sa_parse_calibration_yaml is the file-reading half of ReadObjectYml (FastACVNet_plus_Algorithm.cpp:98-114): all 11
@@ -206,7 +236,9 @@ SA_API int sa_resize_table(int dst, int src, int* table);
  * compaction needs live in a 512 KiB device array built into the library (present on every GPU that loads it, until
  * the process exits).
  *   Limit: ceil(w*h / 1024) * n <= 65536 scratch slots per call (218 frames of 640x480, 32 of 1920x1080, 8 of
- *   3840x2160); beyond that the call returns SA_ERR_TOO_LARGE and explains itself in `err`.
+ *   3840x2160) and n <= 65535 frames; beyond that the call returns SA_ERR_TOO_LARGE and explains itself in `err`.
+ *   `points` must be 8-byte aligned (the rows are written as pairs of floats), `disparity` and `counts` 4-byte aligned;
+ *   otherwise SA_ERR_INVALID_ARG.
  *   All image/point pointers are DEVICE pointers on the CURRENT device (there is no handle to select one); Q16 is 16
  *   host floats, row-major.  Strides of 0 mean "contiguous" (left_pitch = 3*w, frame strides = one frame).
  *   disparity [n][..] float (sign-flipped in place when negate != 0, like RAFTStereo's kernel), left_bgr the rectified

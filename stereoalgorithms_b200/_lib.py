@@ -66,8 +66,12 @@ SIGNATURES = {
     "sa_copy_tensor": (_i, [_vp, _i, _i, _vp, _i, _vp]),
     "sa_copy_disparity": (_i, [_vp, _i, _vp, _i, _vp]),
     "sa_synchronize": (_i, [_vp]),
+    "sa_download": (_i, [_vp, _i, _vp, _vp, _vp, _sz, _vp, _sz, _vp, _vp]),
+    "sa_get_stream": (_vp, [_vp]),
     "sa_set_engine": (_i, [_vp, ENGINE_FN, _vp]),
     "sa_run_batch": (_i, [_vp, _i, _vp, _vp, _i, _u, _vp, _vp, _vp, _vp, _vp]),
+    "sa_run_batch_multi": (_i, [C.POINTER(_vp), _i, _i, _vp, _vp, _i, _u, _vp, _vp, _vp, _vp, _vp, C.POINTER(_i)]),
+    "sa_shard_range": (_i, [_i, _i, _i, C.POINTER(_i), C.POINTER(_i)]),
     "sa_parse_calibration_yaml": (_i, [_cp, C.POINTER(sa_calibration), C.c_char_p, _sz]),
     "sa_write_calibration_yaml": (_i, [_cp, C.POINTER(sa_calibration)]),
     "sa_stereo_rectify": (_i, [_vp, _vp, _i, _vp, _vp, _i, _i, _i, _vp, _vp, _i, C.c_double, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),

@@ -92,8 +92,18 @@ class _Model:
     def SetStubSeed(self, p, seed: int) -> int:
         return self._l().sa_ref_SetStubSeed(p, int(seed))
 
+    def SetEngine(self, p, fn) -> int:
+        """The network slot (sa_ref_SetEngine): fn(stream, first_frame, n, left_tensor_ptr, right_tensor_ptr, disparity_ptr)
+        -> int is called between the two halves of every Run with the handle's stream (an integer cudaStream_t, never 0):
+        enqueue the network on that stream, do not synchronise.  None removes the callback."""
+        if not hasattr(self, "_engines"):
+            self._engines = {}
+        cb = L.ENGINE_FN(lambda user, stream, f0, n, lt, rt, d: int(fn(stream, f0, n, lt, rt, d) or 0)) if fn else L.ENGINE_FN()
+        self._engines[p] = cb          # keep the trampoline alive as long as the handle may call it
+        return self._l().sa_ref_SetEngine(p, cb, None)
+
     def SetHostRegister(self, p, on: bool) -> int:
-        """Page-locking of a reused pointcloud buffer (sa_ref_SetHostRegister); on by default."""
+        """Page-locking of a reused pointcloud buffer (sa_ref_SetHostRegister); off by default."""
         return self._l().sa_ref_SetHostRegister(p, 1 if on else 0)
 
     def Geometry(self, p):

@@ -255,6 +255,7 @@ static int stage_reproject(sa_handle* h, int f0, int n, int mode, float* dev_out
 {
     if (!h->have_q) return fail(h, SA_ERR_NOT_READY, "no Q matrix (load a calibration or call sa_set_Q)");
     if (!h->color_src[0]) return fail(h, SA_ERR_NOT_READY, "no left image on the device (run sa_rectify_preprocess first)");
+    if (!dev_out) return fail(h, SA_ERR_INVALID_ARG, "reproject: no destination for the points (handle created with SA_FLAG_NO_POINT_BUF and no device `out`)");
     const size_t npix = (size_t)h->w * h->h;
     ReprojectArgs a{};
     a.disp = h->disp + (size_t)f0 * disp_frame_floats(h);
@@ -802,6 +803,41 @@ int sa_synchronize(sa_handle* h)
     return SA_OK;
 }
 
+sa_stream sa_get_stream(sa_handle* h) { return h ? (sa_stream)h->stream : nullptr; }
+
+int sa_download(sa_handle* h, int n, float* pointcloud, float* disparity, uint8_t* rect_left, size_t rect_left_pitch, uint8_t* rect_right,
+                size_t rect_right_pitch, uint8_t* heatmap, sa_stream stream)
+{
+    SA_ENTER(h);
+    SA_CHECK_N(h, n);
+    if (n == 0) return SA_OK;
+    cudaStream_t s = pick(h, stream);
+    const size_t npix = (size_t)h->w * h->h, row = (size_t)h->W * 3;
+    if (pointcloud) {
+        if (!h->points) return fail(h, SA_ERR_INVALID_ARG, "sa_download: handle was created without a point buffer");
+        SA_CUDA(h, cudaMemcpyAsync(pointcloud, h->points, (size_t)n * npix * 6 * sizeof(float), cudaMemcpyDeviceToHost, s));
+    }
+    if (disparity)
+        SA_CUDA(h, cudaMemcpy2DAsync(disparity, npix * sizeof(float), h->disp, disp_frame_floats(h) * sizeof(float), npix * sizeof(float), (size_t)n,
+                                     cudaMemcpyDeviceToHost, s));
+    uint8_t* rect_out[2] = {rect_left, rect_right};
+    const size_t rect_out_pitch[2] = {rect_left_pitch ? rect_left_pitch : row, rect_right_pitch ? rect_right_pitch : row};
+    for (int e = 0; e < 2; e++) {
+        if (!rect_out[e]) continue;
+        if (rect_out_pitch[e] < row) return fail(h, SA_ERR_INVALID_ARG, "sa_download: pitch %zu < 3*width = %zu", rect_out_pitch[e], row);
+        const uint8_t* src = h->resize ? h->rect[e] : h->color_src[e];
+        if (!src) return fail(h, SA_ERR_NOT_READY, "sa_download: nothing processed yet");
+        const size_t pitch = h->resize ? h->rect_pitch : h->color_pitch;
+        SA_CUDA(h, cudaMemcpy2DAsync(rect_out[e], rect_out_pitch[e], src, pitch, row, (size_t)n * h->H, cudaMemcpyDeviceToHost, s));
+    }
+    if (heatmap) {
+        if (!h->heat) return fail(h, SA_ERR_INVALID_ARG, "sa_download: handle was created without a heatmap buffer");
+        SA_CUDA(h, cudaMemcpyAsync(heatmap, h->heat, (size_t)n * npix * 3, cudaMemcpyDeviceToHost, s));
+    }
+    SA_CUDA(h, cudaStreamSynchronize(s));
+    return SA_OK;
+}
+
 int sa_set_engine(sa_handle* h, sa_engine_fn fn, void* user)
 {
     if (!h) return SA_ERR_INVALID_ARG;
@@ -819,21 +855,14 @@ static cudaEvent_t pool_event(sa_handle* h, size_t i)
     return h->ev_pool[i];
 }
 
-int sa_run_batch(sa_handle* h, int n, const uint8_t* left, const uint8_t* right, int rectify, unsigned stub_seed, float* pointcloud, float* disparity,
-                 uint8_t* rect_left, uint8_t* rect_right, uint8_t* heatmap)
+// The chunk loop of sa_run_batch.  Returns at the first failure with work possibly still queued on the three streams;
+// the caller drains them before the error reaches the user.
+static int run_batch_chunks(sa_handle* h, int n, const uint8_t* left, const uint8_t* right, int rectify, unsigned stub_seed, float* pointcloud,
+                            float* disparity, uint8_t* rect_left, uint8_t* rect_right, uint8_t* heatmap)
 {
-    SA_ENTER(h);
-    SA_CHECK_N(h, n);
-    if (n == 0) return SA_OK;
-    if (!left || !right) return fail(h, SA_ERR_INVALID_ARG, "sa_run_batch: null image pointer");
-    if (!h->points && pointcloud) return fail(h, SA_ERR_INVALID_ARG, "sa_run_batch: handle was created without a point buffer");
-    if (!h->heat && heatmap) return fail(h, SA_ERR_INVALID_ARG, "sa_run_batch: handle was created without a heatmap buffer");
     const size_t img = (size_t)h->W * h->H * 3, npix = (size_t)h->w * h->h, dfl = disp_frame_floats(h);
     const int chunk = (int)(h->opt_chunk > 0 ? h->opt_chunk : 8);
     const int nchunks = (n + chunk - 1) / chunk;
-    h->n_last = n;
-    h->minmax_valid = 0;
-    h->partial_valid = 0;
     uint8_t* rect_out[2] = {rect_left, rect_right};
     const uint8_t* host_in[2] = {left, right};
     for (int c = 0; c < nchunks; c++) {
@@ -856,7 +885,7 @@ int sa_run_batch(sa_handle* h, int n, const uint8_t* left, const uint8_t* right,
             if (rc != 0) return fail(h, SA_ERR_INVALID_ARG, "sa_run_batch: engine callback returned %d", rc);
         } else if (stub_seed != 0) {
             StageScope t(h, SA_STAGE_STUB, h->stream);
-            SA_CUDA(h, launch_stub(h->disp + (size_t)f0 * dfl, dfl, h->planes, h->w, h->h, f0, m, stub_seed, h->cfg.model == SA_MODEL_RAFTSTEREO, h->stream, &h->launches));
+            SA_CUDA(h, launch_stub(h->disp + (size_t)f0 * dfl, dfl, h->planes, h->w, h->h, f0 + (int)h->opt_frame_base, m, stub_seed, h->cfg.model == SA_MODEL_RAFTSTEREO, h->stream, &h->launches));
         }
         // stage B (+ C)
         rc = stage_reproject(h, f0, m, SA_DENSE, h->points + (size_t)f0 * npix * 6, nullptr, h->stream);
@@ -864,15 +893,51 @@ int sa_run_batch(sa_handle* h, int n, const uint8_t* left, const uint8_t* right,
         if (heatmap) { rc = stage_heatmap(h, f0, m, h->heat + (size_t)f0 * npix * 3, 1, h->stream); if (rc != SA_OK) return rc; }
         SA_CUDA(h, cudaEventRecord(done, h->stream));
         SA_CUDA(h, cudaStreamWaitEvent(h->s_d2h, done, 0));
-        // download (cudaMemcpy D2H x2, TRTFastACVNet_plus.cpp:163-164; plus the rectified images the reference leaves in left/right)
+        // download (cudaMemcpy D2H x2, TRTFastACVNet_plus.cpp:163-164; plus the rectified images the reference leaves in left/right).
+        // One linear copy per output wherever the device layout is dense (single-plane disparity, unpadded rectified rows):
+        // a 2-D copy of h rows costs the copy engine a descriptor per row.
         if (pointcloud) SA_CUDA(h, cudaMemcpyAsync(pointcloud + (size_t)f0 * npix * 6, h->points + (size_t)f0 * npix * 6, (size_t)m * npix * 6 * sizeof(float), cudaMemcpyDeviceToHost, h->s_d2h));
-        if (disparity) SA_CUDA(h, cudaMemcpy2DAsync(disparity + (size_t)f0 * npix, npix * sizeof(float), h->disp + (size_t)f0 * dfl, dfl * sizeof(float), npix * sizeof(float), (size_t)m, cudaMemcpyDeviceToHost, h->s_d2h));
+        if (disparity) {
+            if (h->planes == 1) SA_CUDA(h, cudaMemcpyAsync(disparity + (size_t)f0 * npix, h->disp + (size_t)f0 * dfl, (size_t)m * npix * sizeof(float), cudaMemcpyDeviceToHost, h->s_d2h));
+            else SA_CUDA(h, cudaMemcpy2DAsync(disparity + (size_t)f0 * npix, npix * sizeof(float), h->disp + (size_t)f0 * dfl, dfl * sizeof(float), npix * sizeof(float), (size_t)m, cudaMemcpyDeviceToHost, h->s_d2h));
+        }
         if (rectify)
-            for (int e = 0; e < 2; e++)
-                if (rect_out[e]) SA_CUDA(h, cudaMemcpy2DAsync(rect_out[e] + (size_t)f0 * img, (size_t)h->W * 3, h->rect[e] + (size_t)f0 * h->rect_frame, h->rect_pitch, (size_t)h->W * 3, (size_t)m * h->H, cudaMemcpyDeviceToHost, h->s_d2h));
+            for (int e = 0; e < 2; e++) {
+                if (!rect_out[e]) continue;
+                if (h->rect_pitch == (size_t)h->W * 3) SA_CUDA(h, cudaMemcpyAsync(rect_out[e] + (size_t)f0 * img, h->rect[e] + (size_t)f0 * h->rect_frame, (size_t)m * img, cudaMemcpyDeviceToHost, h->s_d2h));
+                else SA_CUDA(h, cudaMemcpy2DAsync(rect_out[e] + (size_t)f0 * img, (size_t)h->W * 3, h->rect[e] + (size_t)f0 * h->rect_frame, h->rect_pitch, (size_t)h->W * 3, (size_t)m * h->H, cudaMemcpyDeviceToHost, h->s_d2h));
+            }
         if (heatmap) SA_CUDA(h, cudaMemcpyAsync(heatmap + (size_t)f0 * npix * 3, h->heat + (size_t)f0 * npix * 3, (size_t)m * npix * 3, cudaMemcpyDeviceToHost, h->s_d2h));
     }
-    // colour / rectified pointers describe frame 0 of the whole batch
+    return SA_OK;
+}
+
+int sa_run_batch(sa_handle* h, int n, const uint8_t* left, const uint8_t* right, int rectify, unsigned stub_seed, float* pointcloud, float* disparity,
+                 uint8_t* rect_left, uint8_t* rect_right, uint8_t* heatmap)
+{
+    SA_ENTER(h);
+    SA_CHECK_N(h, n);
+    if (n == 0) return SA_OK;
+    if (!left || !right) return fail(h, SA_ERR_INVALID_ARG, "sa_run_batch: null image pointer");
+    // stage B always writes the cloud (its min/max partials feed the heat map), so the internal buffer is needed even when
+    // the caller wants only the disparity or the heat map back
+    if (!h->points) return fail(h, SA_ERR_INVALID_ARG, "sa_run_batch: handle was created without a point buffer (SA_FLAG_NO_POINT_BUF)");
+    if (!h->heat && heatmap) return fail(h, SA_ERR_INVALID_ARG, "sa_run_batch: handle was created without a heatmap buffer");
+    h->n_last = n;
+    h->minmax_valid = 0;
+    h->partial_valid = 0;
+    const int rc = run_batch_chunks(h, n, left, right, rectify, stub_seed, pointcloud, disparity, rect_left, rect_right, heatmap);
+    if (rc != SA_OK) {
+        // Earlier chunks may still be copying into the caller's buffers: nothing of this call is in flight once it returns,
+        // also on failure.  (The message of the first failure is kept.)
+        const std::string first = h->err;
+        cudaStreamSynchronize(h->s_h2d);
+        cudaStreamSynchronize(h->stream);
+        cudaStreamSynchronize(h->s_d2h);
+        cudaGetLastError();
+        h->err = first;
+        return rc;
+    }
     SA_CUDA(h, cudaStreamSynchronize(h->s_d2h));
     SA_CUDA(h, cudaStreamSynchronize(h->stream));
     h->partial_valid = n;
@@ -955,6 +1020,7 @@ int sa_set_option(sa_handle* h, const char* key, long value)
     else if (!std::strcmp(key, "no_fixed_size")) h->opt_no_fixed_size = value;
     else if (!std::strcmp(key, "scalar_preprocess")) h->opt_scalar_preprocess = value;
     else if (!std::strcmp(key, "l2_prefetch")) h->opt_l2_prefetch = value;
+    else if (!std::strcmp(key, "frame_base")) h->opt_frame_base = value;
     else if (!std::strcmp(key, "chunk_taper")) h->opt_chunk_taper = value < 0 ? 0 : (value > 95 ? 95 : value);
     else return fail(h, SA_ERR_INVALID_ARG, "sa_set_option: unknown key '%s'", key);
     return SA_OK;

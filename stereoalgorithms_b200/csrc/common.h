@@ -112,6 +112,7 @@ struct sa_handle {
     long opt_l2_prefetch = -1;        // see RectifyArgs::l2_prefetch; -1 = automatic
     long opt_bulk = 0;                // rectify_tma_kernel when the frames are 16-byte aligned
     long opt_batch_loop = 1;          // rectify_batch_kernel (default); 0 = one CTA per (tile, eye, frame)
+    long opt_frame_base = 0;          // global index of this handle's frame 0 (sa_run_batch_multi: the stub numbers frames across shards)
     int sm_count = 148;
 
     long launches = 0;

@@ -24,7 +24,7 @@ struct Algorithm {
     std::string err;
     std::vector<uint8_t> tmp;
     // page-locking of a point-cloud buffer the caller reuses (sa_ref_SetHostRegister)
-    bool host_register = true;
+    bool host_register = false;    // opt-in: see sa_ref_SetHostRegister
     float* pc_seen = nullptr;      // pointer of the previous Run
     float* pc_reg = nullptr;       // registered pointer ...
     size_t pc_reg_bytes = 0;       // ... and its size
@@ -134,34 +134,24 @@ int sa_ref_Run(void* p, int rectify, sa_image* left, sa_image* right, float* poi
         if (rc == SA_OK) rc = sa_synchronize(g);
     }
     if (rc != SA_OK) { a->err = sa_last_error(g); return -1; }
-    // network slot
+    // network slot: context->enqueueV3(stream) (TRTFastACVNet_plus.cpp:152).  The callback gets the stream stage A was queued
+    // on and stage B will be queued on (the handle's own, never NULL), so an engine enqueued there is ordered after the
+    // tensors are written and before the disparity is read - without the cudaStreamSynchronize of the reference (:159).
     if (a->engine) {
-        rc = a->engine(a->engine_user, nullptr, 0, 1, sa_input_tensor(g, SA_LEFT), sa_input_tensor(g, SA_RIGHT), sa_disparity_buffer(g));
-        if (rc != 0) { a->err = "engine callback failed"; return -1; }
+        rc = a->engine(a->engine_user, sa_get_stream(g), 0, 1, sa_input_tensor(g, SA_LEFT), sa_input_tensor(g, SA_RIGHT), sa_disparity_buffer(g));
+        if (rc != 0) { a->err = "engine callback failed"; sa_synchronize(g); return -1; }
     } else if (a->stub_seed != 0) {
         rc = sa_stub_disparity(g, 1, a->stub_seed, nullptr);
         if (rc != SA_OK) { a->err = sa_last_error(g); return -1; }
     }
     track_pointcloud_buffer(a, pointcloud, (size_t)W * H * 6 * sizeof(float));
-    rc = sa_reproject(g, 1, SA_DENSE, pointcloud, nullptr, SA_HOST, nullptr);
+    rc = sa_reproject(g, 1, SA_DENSE, nullptr, nullptr, SA_DEVICE, nullptr);           // cloud stays in the internal buffer ...
+    if (rc != SA_OK) { a->err = sa_last_error(g); sa_synchronize(g); return -1; }
+    // ... and every read-back of the call is queued behind it and waited for once (the reference: two blocking cudaMemcpy,
+    // :163-164).  cv::remap(img, img, ...) leaves the rectified image in the caller's Mat (FastACVNet_plus_Algorithm.cpp:142-143):
+    // copied straight into its rows, whatever their step.
+    rc = sa_download(g, 1, pointcloud, disparity, rectify ? left->data : nullptr, lstep, rectify ? right->data : nullptr, rstep, nullptr, nullptr);
     if (rc != SA_OK) { a->err = sa_last_error(g); return -1; }
-    if (disparity) {
-        rc = sa_copy_disparity(g, 1, disparity, SA_HOST, nullptr);
-        if (rc != SA_OK) { a->err = sa_last_error(g); return -1; }
-    }
-    if (rectify) {   // cv::remap(img, img, ...) leaves the rectified image in the caller's Mat (:142-143)
-        sa_image* im[2] = {left, right};
-        const size_t st[2] = {lstep, rstep};
-        for (int e = 0; e < 2; e++) {
-            if (st[e] == row) rc = sa_copy_rectified(g, 1, e, im[e]->data, SA_HOST, nullptr);
-            else {
-                a->tmp.resize(row * H);
-                rc = sa_copy_rectified(g, 1, e, a->tmp.data(), SA_HOST, nullptr);
-                if (rc == SA_OK) for (int y = 0; y < H; y++) std::memcpy(im[e]->data + (size_t)y * st[e], &a->tmp[y * row], row);
-            }
-            if (rc != SA_OK) { a->err = sa_last_error(g); return -1; }
-        }
-    }
     return 0;
 }
 

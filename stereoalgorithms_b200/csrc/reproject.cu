@@ -50,8 +50,10 @@ __device__ __forceinline__ float rcp_approx(float x)
 //   FAST: r = rcp(w) refined by one Newton step, then q = n*r corrected with the exact remainder (two FMAs): the result
 //   is within 1 ulp of the IEEE quotient (the parity gate for XYZ is 1e-5 relative), without the ~60-instruction slow
 //   path that a division by zero takes - and ~5 % of real disparities are zero.  w = 0, inf, NaN: n * rcp(w) is IEEE's
-//   answer in kind and sign (n/0 = +-inf, 0/0 = NaN, n/inf = 0).  |w| outside [2^-100, 2^100] otherwise: exact division.
-//   The host only selects FAST when every Q entry used is finite and small enough that the numerators stay below 2^36.
+//   answer in kind and sign (n/0 = +-inf, 0/0 = NaN, n/inf = 0).  |w| outside [2^-60, 2^60] otherwise: exact division.
+//   The host only selects FAST when every Q entry used is finite and small enough that the numerators stay below 2^36,
+//   so inside that window a quotient is at most 2^96: n * r1 cannot overflow to inf (and then turn the correction step
+//   into inf - inf = NaN where IEEE division answers +-inf), and r1 is never a flushed denormal.
 //   !FAST: three IEEE divisions, each product and sum rounded once - bit-identical to the reference arithmetic without
 //   FMA contraction.
 template <bool FAST>
@@ -64,7 +66,7 @@ __device__ __forceinline__ void point_xyz(const Q10& q, float d, float fc, float
     if (FAST) {
         const float aw = fabsf(w);
         float r = rcp_approx(w);
-        const bool common = aw >= 0x1p-100f && aw <= 0x1p100f;
+        const bool common = aw >= 0x1p-60f && aw <= 0x1p60f;
         const bool special = aw == 0.0f || !(aw < INFINITY);
         if (common || special) {
             const float e = fmaf(-w, r, 1.0f);
@@ -499,7 +501,12 @@ extern "C" int sa_reproject_compact_noalloc(float* disparity, size_t disparity_f
     if (left_pitch < (size_t)w * 3) return noalloc_fail(err, err_len, SA_ERR_INVALID_ARG, "sa_reproject_compact_noalloc: left_pitch %zu < 3*w", left_pitch);
     if (disparity_frame_stride == 0) disparity_frame_stride = (size_t)w * h;
     if (left_frame_stride == 0) left_frame_stride = left_pitch * (size_t)h;
+    if (reinterpret_cast<uintptr_t>(points) % 8 != 0 || reinterpret_cast<uintptr_t>(disparity) % 4 != 0 || reinterpret_cast<uintptr_t>(counts) % 4 != 0)
+        return noalloc_fail(err, err_len, SA_ERR_INVALID_ARG,
+                            "sa_reproject_compact_noalloc: points must be 8-byte aligned (rows leave as float2 stores), disparity and counts 4-byte aligned");
     const long long nblk = reproject_blocks_per_frame(w, h);
+    if (n > 65535)   // one grid row per frame; small frames would otherwise pass the slot limit below and fail as an opaque launch error
+        return noalloc_fail(err, err_len, SA_ERR_TOO_LARGE, "sa_reproject_compact_noalloc: %d frames in one call, the limit is 65535; split the call", n);
     if (nblk * n > kNoAllocMaxBlocks)
         return noalloc_fail(err, err_len, SA_ERR_TOO_LARGE,
                             "sa_reproject_compact_noalloc: %d frames of %dx%d need %lld scratch slots, the built-in scratch holds %d "

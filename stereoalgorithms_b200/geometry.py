@@ -226,6 +226,23 @@ class StereoGeometry:
     def synchronize(self):
         self._check(self._lib.sa_synchronize(self._h))
 
+    @property
+    def stream(self) -> int:
+        """The handle's own compute stream (sa_get_stream) as an integer cudaStream_t."""
+        return int(self._lib.sa_get_stream(self._h) or 0)
+
+    def download(self, n: int, pointcloud=None, disparity=None, rect_left=None, rect_right=None, heatmap=None, stream=None):
+        """sa_download: every requested read-back (host numpy arrays) queued on one stream, one synchronisation."""
+        def img(a):          # [n, H, W, 3] uint8 whose rows may be padded (a view of a wider array), frames H rows apart
+            if a is None:
+                return None, 0
+            if a.strides[-1] != 1 or a.strides[-2] != 3 or (a.ndim == 4 and a.strides[0] != a.strides[1] * self.H):
+                raise ValueError("rectified image destination: packed pixels, frames H rows apart")
+            return a.ctypes.data, int(a.strides[-3])
+        (pl, sl), (pr, sr) = img(rect_left), img(rect_right)
+        ptrs = [_ptr(x)[0] for x in (pointcloud, disparity, heatmap)]
+        self._check(self._lib.sa_download(self._h, n, ptrs[0], ptrs[1], pl, sl, pr, sr, ptrs[2], stream))
+
     # -- whole path with host buffers ----------------------------------------------------------------------------
     def set_engine(self, fn):
         """fn(stream, first_frame, n, left_tensor_ptr, right_tensor_ptr, disparity_ptr) -> int, or None."""
@@ -258,6 +275,20 @@ class StereoGeometry:
 
     def set_option(self, key: str, value: int):
         self._check(self._lib.sa_set_option(self._h, key.encode(), int(value)))
+
+
+def run_batch_multi(geoms, left, right, n: int, rectify: bool = True, stub_seed: int = 0, pointcloud=None, disparity=None,
+                    rect_left=None, rect_right=None, heatmap=None):
+    """sa_run_batch_multi: one host batch of n pairs cut frame-wise over the handles in ``geoms`` (one per GPU), each shard on
+    its own host thread.  All buffers are HOST memory with the layouts of ``StereoGeometry.run_batch``."""
+    lib = L.load()
+    arr = (C.c_void_p * len(geoms))(*[g.handle for g in geoms])
+    ptrs = [_ptr(x)[0] for x in (left, right, pointcloud, disparity, rect_left, rect_right, heatmap)]
+    failed = C.c_int(-1)
+    rc = lib.sa_run_batch_multi(arr, len(geoms), n, ptrs[0], ptrs[1], 1 if rectify else 0, stub_seed, *ptrs[2:], C.byref(failed))
+    if rc != L.SA_OK:
+        msg = (lib.sa_last_error(geoms[failed.value].handle) or b"").decode() if failed.value >= 0 else "invalid argument"
+        raise StereoGeomError(rc, f"shard {failed.value}: {msg}")
 
 
 class PinnedArray:

@@ -9,7 +9,7 @@ from __future__ import annotations
 
 def shard_range(n_total: int, rank: int, world: int) -> tuple[int, int]:
     """[begin, end) of the pairs rank `rank` owns: contiguous blocks of ceil(n_total / world), the last ones shorter
-    (possibly empty)."""
+    (possibly empty).  Same partition as the library's sa_shard_range / sa_run_batch_multi (tests/test_multi_rank_cpu.py)."""
     if world <= 0 or not (0 <= rank < world) or n_total < 0:
         raise ValueError(f"bad shard request: n_total={n_total} rank={rank} world={world}")
     per = -(-n_total // world)

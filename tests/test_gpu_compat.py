@@ -56,13 +56,14 @@ def test_demo_main_fastacvnet_plus(demo_pair, calibs, tmp_path):
 
 
 def test_reused_pointcloud_buffer_is_page_locked_and_results_do_not_change(demo_pair, calibs):
-    """The demos pass the same `pointcloud` to every Run (FastACVNet_plus/test/main.cpp:40-50); from the second call on the
-    library page-locks it.  Results must not depend on that, on switching buffers, or on switching the feature off."""
+    """The demos pass the same `pointcloud` to every Run (FastACVNet_plus/test/main.cpp:40-50); with SetHostRegister(1) the
+    library page-locks it from the second call on.  Results must not depend on that, on switching buffers, or on switching the feature off."""
     from stereoalgorithms_b200 import _lib as L
     from stereoalgorithms_b200.compat import FastACVNet_plus as F, Mat
     lib = L.load()
     imageL, imageR = demo_pair
     p = F.Initialize("m.onnx", 0, CALIB)
+    assert F.SetHostRegister(p, True) == 0                   # opt-in: the caller promises not to free a pinned buffer early
     n = imageL.shape[0] * imageL.shape[1] * 6
     bufs = [np.zeros(n, np.float32), np.zeros(n, np.float32)]
     d = Mat()
@@ -170,3 +171,63 @@ def test_cpp_shim_demo_program(demo_pair, calibs, tmp_path):
     pts = np.fromfile(str(tmp_path / "o_pointcloud.f32"), np.float32).reshape(-1, 6)
     want, _ = O.reproject_dense(O.FASTACVNET_PLUS, d, rl, c["Q"])
     _check_points(pts, want)
+
+
+def test_engine_on_the_reference_named_path_is_ordered_on_the_handle_stream(demo_pair, calibs):
+    """sa_ref_SetEngine: the slot of context->enqueueV3(stream) between preprocess and reproject
+    (FastACVNet_plus/src/TRTFastACVNet_plus.cpp:133-160), through Run<Model>_RectifyImage.  The callback is handed the
+    stream both halves run on.  It behaves like an asynchronous engine: it snapshots the tensors it was given with a
+    stream-ordered copy, keeps the stream busy with a long spin kernel, and only then writes the 'network output' - all
+    without synchronising.  Stage B must wait for that write (the cloud equals the oracle's for THIS disparity, twice in a
+    row with different outputs), and the snapshot must already hold the finished tensors.  With a NULL stream handed to the
+    callback - work on the legacy default stream, which the handle's non-blocking stream does not order against - this fails."""
+    import torch
+    from cuda.bindings import runtime as rt
+    from stereoalgorithms_b200.compat import FastACVNet_plus as F, Mat
+    c = calibs["calib_b"]
+    W, H = 640, 480
+    imageL, imageR = demo_pair
+    nbytes = W * H * 4
+    snap = [torch.zeros(3 * H * W, dtype=torch.float32, device="cuda") for _ in range(2)]
+    net_out = torch.zeros(H * W, dtype=torch.float32, device="cuda")
+    torch.cuda.synchronize()
+    seen = []
+    D2D = rt.cudaMemcpyKind.cudaMemcpyDeviceToDevice
+
+    def engine(stream, first_frame, n, left_tensor, right_tensor, disparity):
+        s = int(stream or 0)
+        seen.append(s)
+        ok = rt.cudaError_t.cudaSuccess
+        for buf, src in zip(snap, (left_tensor, right_tensor)):
+            if rt.cudaMemcpyAsync(buf.data_ptr(), src, 3 * nbytes, D2D, s)[0] != ok:
+                return 1
+        with torch.cuda.stream(torch.cuda.ExternalStream(s)):
+            torch.cuda._sleep(100_000_000)                               # ~50 ms of spinning on the stream we were given
+        return 0 if rt.cudaMemcpyAsync(disparity, net_out.data_ptr(), nbytes, D2D, s)[0] == ok else 1
+
+    p = F.Initialize("m.onnx", 0, CALIB)
+    assert F.SetEngine(p, engine) == 0
+    rl, rr = O.rectify_pair(c, imageL, imageR)
+    tl, tr = O.preprocess(O.FASTACVNET_PLUS, rl, rr)
+    pointcloud = np.empty(W * H * 6, np.float32)
+    disparity = Mat()
+    for k in range(2):
+        D = O.synthetic_disparity(W, H, 500 + k)
+        net_out.copy_(torch.from_numpy(D).reshape(-1).cuda())
+        torch.cuda.synchronize()
+        l, r = imageL.copy(), imageR.copy()
+        assert F.RunFastACVNet_plus_RectifyImage(p, l, r, pointcloud, disparity) == 0
+        assert seen[-1] != 0, "the engine callback must be given the handle's stream, not NULL"
+        assert np.array_equal(l, rl) and np.array_equal(r, rr)
+        assert np.array_equal(disparity.array, D)
+        want, _ = O.reproject_dense(O.FASTACVNET_PLUS, D, rl, c["Q"])
+        _check_points(pointcloud.reshape(-1, 6), want)
+        torch.cuda.synchronize()
+        assert np.array_equal(snap[0].cpu().numpy().reshape(3, H, W), tl) and np.array_equal(snap[1].cpu().numpy().reshape(3, H, W), tr)
+    # an engine that fails: Run returns -1, the next Run without the engine works again
+    assert F.SetEngine(p, lambda *a: 7) == 0
+    assert F.RunFastACVNet_plus_RectifyImage(p, imageL.copy(), imageR.copy(), pointcloud, disparity) == -1
+    assert "engine" in F.LastError(p)
+    assert F.SetEngine(p, None) == 0
+    assert F.RunFastACVNet_plus_RectifyImage(p, imageL.copy(), imageR.copy(), pointcloud, disparity) == 0
+    assert F.Release(p) == 0

@@ -152,6 +152,50 @@ def test_rectified_batch_device_input_and_pitch(calibs, demo_pair):
         assert np.array_equal(g.rectified(n, 0), want_l) and np.array_equal(g.rectified(n, 1), want_r)
 
 
+def test_the_benchmarked_configuration_itself(calibs, demo_pair):
+    """BASELINE configs[1] exactly as bench.py runs it: 64 pairs of 640x480, RAFTStereo, f16 tensors, every option at its
+    default, device-resident input, stage A then stage B back to back on a caller-owned stream (the multi-chunk, tapered
+    schedule a 64-pair batch gets; the <F16, IDENT, 640, 480> instantiation).  A sample of the frames - the first and last
+    frame of every chunk region among them - is checked against the oracle: rectified images and f16 tensors exactly, the
+    flipped disparity exactly, XYZ within the gate."""
+    import torch
+    from stereoalgorithms_b200.geometry import DENSE, F16
+    c = calibs["calib_a"]
+    n, W, H = 64, 640, 480
+    L = np.empty((n, H, W, 3), np.uint8)
+    R = np.empty((n, H, W, 3), np.uint8)
+    for i in range(n):                                        # bench.py:make_inputs - the demo pair plus +-8 noise, seed = frame
+        rng = np.random.default_rng(i)
+        L[i] = np.clip(demo_pair[0].astype(np.int16) + rng.integers(-8, 9, demo_pair[0].shape), 0, 255)
+        R[i] = np.clip(demo_pair[1].astype(np.int16) + rng.integers(-8, 9, demo_pair[1].shape), 0, 255)
+    D = np.stack([-O.synthetic_disparity(W, H, 900 + i) for i in range(n)])    # the RAFT network emits the negated disparity
+    stream = torch.cuda.Stream()
+    with geom(W, H, model="RAFTStereo", dtype=F16, max_batch=n) as g:
+        g.set_calibration(c)
+        with torch.cuda.stream(stream):
+            dL, dR = torch.from_numpy(L).cuda(), torch.from_numpy(R).cuda()
+            g.set_disparity(torch.from_numpy(D[:, None]).cuda(), n=n, stream=stream.cuda_stream)
+            for _ in range(2):                                # twice: the sign flip is written back, so flip it back in between
+                g.rectify_preprocess(dL, dR, n=n, stream=stream.cuda_stream)
+                g.reproject(n, DENSE, to_host=False, stream=stream.cuda_stream)
+            g.reproject(n, DENSE, to_host=False, stream=stream.cuda_stream)   # odd number of flips in total: disparity is +d now
+        stream.synchronize()
+        rl, rr = g.rectified(n, 0), g.rectified(n, 1)
+        tl, tr = g.tensor(n, 0), g.tensor(n, 1)
+        disp = g.disparity(n)
+        pts = np.empty((n, W * H, 6), np.float32)
+        g.download(n, pointcloud=pts)
+    assert np.array_equal(disp, -D)
+    (l1, l2), (r1, r2) = O.rectify_maps(c, (W, H))
+    for i in (0, 1, 11, 12, 13, 26, 27, 31, 32, 40, 52, 62, 63):
+        wl, wr = OC.remap(L[i], l1, l2), OC.remap(R[i], r1, r2)
+        assert np.array_equal(rl[i], wl) and np.array_equal(rr[i], wr), i
+        a, b = O.preprocess(O.RAFTSTEREO, wl, wr, np.float16)
+        assert np.array_equal(tl[i], a) and np.array_equal(tr[i], b), i
+        want, _ = O.reproject_dense(O.RAFTSTEREO, D[i], wl, c["Q"])
+        assert_close_points(pts[i], want, f"bench configuration, frame {i}")
+
+
 # ---- a4 / a10: tensors -----------------------------------------------------------------------------------------
 @pytest.mark.parametrize("model", ["RAFTStereo", "HitNet", "CREStereo", "FastACVNet_plus"])
 @pytest.mark.parametrize("dtype", ["f32", "f16"])
@@ -562,6 +606,30 @@ def test_reproject_special_disparities(calibs):
             wc, k, _ = O.reproject_compact(O.HITNET, d[0, 0], img, c["Q"])
             assert cc[0] == k
             assert_close_points(cp[0, :k], wc, "special values compact")
+
+
+def test_reproject_tiny_disparities_with_large_Q(demo_pair):
+    """Quotients that overflow: with Q entries near the 2^20 limit of the shared-reciprocal path the numerators reach 2^30, and
+    a disparity around 2^-99 makes n/w exceed FLT_MAX.  IEEE division answers +-inf there; the fast path must too (its
+    correction step would otherwise evaluate inf - inf = NaN), and on both sides of the window where it hands over to the
+    exact division (|w| = 2^-60, 2^60) results must stay within the gate."""
+    from stereoalgorithms_b200.geometry import DENSE
+    W, H = 640, 480
+    Q = np.array([[1.0e6, 3.0e5, 0, -2.9e5], [-2.0e5, 9.9e5, 0, 1.0e6], [1.0e3, -2.0e3, 0, 5.4e5], [0, 0, 1.0, 0]])
+    vals = np.array([2.0 ** -99, -2.0 ** -99, 1.7e-30, 2.0 ** -98, 1e-31, 1e-29, 1e-28, 2.0 ** -100, 2.0 ** -101, 2.0 ** -60, 2.0 ** -61, 1.5 * 2.0 ** -60,
+                     2.0 ** 60, 2.0 ** 61, 0.75 * 2.0 ** 60, 1e-20, 1e20, 3.0, 2.0 ** -126, 1e-38], np.float32)
+    d = np.resize(vals, H * W).reshape(H, W).astype(np.float32)
+    img = demo_pair[0]
+    for exact in (0, 1):
+        with geom(W, H) as g:
+            g.set_Q(Q)
+            g.set_option("exact_div", exact)
+            g.rectify_preprocess(img[None], img[None], rectify=False)
+            g.set_disparity(d[None, None])
+            pts, _ = g.reproject(1, DENSE)
+            want, _ = O.reproject_dense(O.FASTACVNET_PLUS, d, img, Q)
+            assert np.isinf(want[:, :3]).any() and np.isfinite(want[:, :3]).any()
+            assert_close_points(pts[0], want, f"tiny disparities, exact_div={exact}")
 
 
 def test_side_by_side_capture_frame(calibs, demo_pair):

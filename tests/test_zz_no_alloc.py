@@ -5,7 +5,10 @@ TensorRT plugin's enqueue(), a real-time callback that must not allocate after s
 the GPU): its compaction scratch is an array built into the library instead of buffers a handle allocated.  It runs the
 same kernels, so its output must equal the handle-based entry point's - checked here with the tolerance the other
 reprojection tests use (1e-5 relative on XYZ, counts / order / colours exact), on two calls in a row with different
-data so that whatever the first call left in the shared scratch cannot leak into the second.
+data so that whatever the first call left in the shared scratch cannot leak into the second.  So that it does not stand
+on another CUDA path alone, every result is also compared with the CPU oracle's compaction (oracle.reproject_compact),
+and a second test drives the options the first leaves at their defaults: a caller-owned stream, a left image with padded
+rows, explicit frame strides.
 
 This file is named to be collected last: if it fails under `pytest -x`, every other test has already run.
 """
@@ -13,6 +16,8 @@ import ctypes as C
 
 import numpy as np
 import pytest
+
+from oracle import oracle as O
 
 pytestmark = pytest.mark.gpu
 
@@ -75,6 +80,51 @@ def test_noalloc_matches_handle_entry_point_twice(negate):
                 _close(got_pts[i, :k], want_pts[i, :k])
                 assert np.array_equal(got_pts[i, :k, 3:], want_pts[i, :k, 3:])   # same pixels, same order
                 assert not got_pts[i, k:].any()
+                # and against the CPU oracle, so the entry point is checked by something that is not a CUDA kernel
+                o_pts, o_cnt, o_d = O.reproject_compact(O.RAFTSTEREO if negate else O.FASTACVNET_PLUS, d[i], img[i], Q)
+                assert o_cnt == k
+                _close(got_pts[i, :k], o_pts)
+                assert np.array_equal(got_pts[i, :k, 3:], o_pts[:, 3:])
+                assert np.array_equal(got_d[i], o_d, equal_nan=True)
+
+
+def test_noalloc_caller_stream_pitched_left_image_and_frame_strides():
+    """The arguments the first test leaves at 0 / NULL: work queued on the caller's own stream (nothing synchronised by the
+    library), left images whose rows are padded (a region of a wider capture buffer), disparity frames further apart than one
+    frame (plane 0 of a two-plane network output).  640x480 takes the vector paths.  Checked against the CPU oracle, twice."""
+    import torch
+    from stereoalgorithms_b200 import _lib as L
+    lib = L.load()
+    torch.cuda.set_device(0)
+    n, W, H = 4, 640, 480
+    pitch = 3 * W + 64
+    Q = np.array([[1, 0, 0, -310.5], [0, 1, 0, -251.25], [0, 0, 0, 517.8], [0, 0, 0.0166, 0]], np.float64)
+    qf = np.ascontiguousarray(Q.reshape(16).astype(np.float32))
+    stream = torch.cuda.Stream()
+    for call in range(2):
+        img, d = _inputs(300 + call, n, W, H)
+        wide = np.full((n, H, pitch), 0xAB, np.uint8)                     # padding bytes that must never show up as colours
+        wide[:, :, :3 * W] = img.reshape(n, H, 3 * W)
+        two_plane = np.full((n, 2, H, W), np.nan, np.float32)
+        two_plane[:, 0] = d
+        with torch.cuda.stream(stream):                                   # inputs are produced on the caller's stream too
+            dd = torch.from_numpy(two_plane).cuda(non_blocking=False)
+            di = torch.from_numpy(wide).cuda()
+            pts = torch.zeros((n, W * H, 6), dtype=torch.float32, device="cuda")
+            cnt = torch.full((n,), -1, dtype=torch.int32, device="cuda")
+            err = C.create_string_buffer(256)
+            rc = lib.sa_reproject_compact_noalloc(dd.data_ptr(), 2 * W * H, di.data_ptr(), pitch, pitch * H, qf.ctypes.data, W, H, n, 0,
+                                                  pts.data_ptr(), cnt.data_ptr(), stream.cuda_stream, err, 256)
+            assert rc == 0, err.value
+        stream.synchronize()
+        got_cnt, got_pts, got_d = cnt.cpu().numpy(), pts.cpu().numpy(), dd.cpu().numpy()
+        assert np.array_equal(got_d[:, 0], d, equal_nan=True) and np.isnan(got_d[:, 1]).all()   # plane 1 untouched
+        for i in range(n):
+            o_pts, o_cnt, _ = O.reproject_compact(O.FASTACVNET_PLUS, d[i], img[i], Q)
+            assert got_cnt[i] == o_cnt
+            _close(got_pts[i, :o_cnt], o_pts)
+            assert np.array_equal(got_pts[i, :o_cnt, 3:], o_pts[:, 3:])
+            assert not got_pts[i, o_cnt:].any()
 
 
 def test_noalloc_rejects_oversize_and_bad_arguments():
@@ -91,6 +141,14 @@ def test_noalloc_rejects_oversize_and_bad_arguments():
                                           buf.data_ptr(), buf.data_ptr(), None, err, 512)
     assert rc == L.SA_ERR_TOO_LARGE
     assert b"65536" in err.value and b"72900" in err.value
+    # tiny frames pass the slot limit with more frames than a grid has rows: still a clear SA_ERR_TOO_LARGE, not a launch error
+    rc = lib.sa_reproject_compact_noalloc(buf.data_ptr(), 0, buf.data_ptr(), 0, 0, q.ctypes.data, 32, 32, 65536, 0,
+                                          buf.data_ptr(), buf.data_ptr(), None, err, 512)
+    assert rc == L.SA_ERR_TOO_LARGE and b"65535" in err.value
+    # the point rows are written as float2: a destination at a 4-byte offset is refused instead of faulting
+    rc = lib.sa_reproject_compact_noalloc(buf.data_ptr(), 0, buf.data_ptr(), 0, 0, q.ctypes.data, 8, 8, 1, 0,
+                                          buf.data_ptr() + 4, buf.data_ptr(), None, err, 512)
+    assert rc == L.SA_ERR_INVALID_ARG and b"aligned" in err.value
     rc = lib.sa_reproject_compact_noalloc(None, 0, buf.data_ptr(), 0, 0, q.ctypes.data, 64, 16, 1, 0, buf.data_ptr(), buf.data_ptr(), None, err, 512)
     assert rc == L.SA_ERR_INVALID_ARG and b"null" in err.value
     rc = lib.sa_reproject_compact_noalloc(buf.data_ptr(), 0, buf.data_ptr(), 10, 0, q.ctypes.data, 64, 16, 1, 0, buf.data_ptr(), buf.data_ptr(), None, err, 512)
