@@ -123,6 +123,43 @@ void oc_preprocess(int model, const uint8_t* img, int H, int W, float* out)
     }
 }
 
+/* float -> IEEE half, round to nearest even (what __float2half_rn / numpy astype(float16) do), integer arithmetic only */
+static uint16_t f32_to_f16(float f)
+{
+    union { float f; uint32_t u; } v, magic;
+    v.f = f;
+    magic.u = ((127u - 15u) + (23u - 10u) + 1u) << 23;
+    const uint32_t sign = v.u & 0x80000000u;
+    uint16_t o;
+    v.u ^= sign;
+    if (v.u >= ((127u + 16u) << 23)) o = (v.u > (255u << 23)) ? 0x7e00 : 0x7c00;       /* NaN : overflow -> inf */
+    else if (v.u < (113u << 23)) { v.f += magic.f; o = (uint16_t)(v.u - magic.u); }      /* half subnormal / zero */
+    else { const uint32_t odd = (v.u >> 13) & 1u; v.u += ((15u - 127u) << 23) + 0xfffu; v.u += odd; o = (uint16_t)(v.u >> 13); }
+    return (uint16_t)(o | (sign >> 16));
+}
+
+/* extension a10: the same kernel-body arithmetic, each value then rounded once to half (out: [3][H][W] as uint16 bit patterns) */
+void oc_preprocess_f16(int model, const uint8_t* img, int H, int W, uint16_t* out)
+{
+    size_t area = (size_t)H * W;
+#pragma omp parallel for schedule(static)
+    for (int dy = 0; dy < H; dy++) {
+        for (int dx = 0; dx < W; dx++) {
+            const uint8_t* v = img + ((size_t)dy * W + dx) * 3;
+            float c0 = v[0], c1 = v[1], c2 = v[2];
+            if (model == OC_HITNET) { c0 = (float)v[0] / 255.0; c1 = (float)v[1] / 255.0; c2 = (float)v[2] / 255.0; }
+            float t = c2; c2 = c0; c0 = t;                       /* bgr -> rgb */
+            if (model == OC_FASTACV) {
+                c0 = (c0 / 255.0f - 0.485) / 0.229;
+                c1 = (c1 / 255.0f - 0.456) / 0.224;
+                c2 = (c2 / 255.0f - 0.406) / 0.225;
+            }
+            uint16_t* p = out + (size_t)dy * W + dx;
+            p[0] = f32_to_f16(c0); p[area] = f32_to_f16(c1); p[2 * area] = f32_to_f16(c2);
+        }
+    }
+}
+
 /* disparity [H][W] f32 (negated in place for RAFT), left [H][W][3] BGR u8, Q[16] f32 -> points [H*W][6] */
 void oc_reproject(int model, float* disparity, const uint8_t* left, const float* Q, int H, int W, float* points)
 {

@@ -22,6 +22,7 @@ def lib():
         L.oc_init_maps.argtypes = [vp, vp, ci, vp, vp, ci, ci, ci, vp, vp]
         L.oc_remap.argtypes = [vp, ci, ci, vp, vp, ci, ci, vp]
         L.oc_preprocess.argtypes = [ci, vp, ci, ci, vp]
+        L.oc_preprocess_f16.argtypes = [ci, vp, ci, ci, vp]
         L.oc_reproject.argtypes = [ci, vp, vp, vp, ci, ci, vp]
         L.oc_compact.argtypes = [vp, vp, C.c_long, vp]
         L.oc_compact.restype = C.c_long
@@ -66,9 +67,13 @@ def remap(src, map1, map2):
     return dst
 
 
-def preprocess_eye(model, img):
+def preprocess_eye(model, img, dtype=np.float32):
     img = _c(img, np.uint8)
     H, W = img.shape[:2]
+    if np.dtype(dtype) == np.float16:                      # extension a10: rounded once to half
+        out = np.empty((3, H, W), np.float16)
+        lib().oc_preprocess_f16(int(model), _p(img), H, W, _p(out))
+        return out
     out = np.empty((3, H, W), np.float32)
     lib().oc_preprocess(int(model), _p(img), H, W, _p(out))
     return out

@@ -727,6 +727,58 @@ def test_rectified_long_batches_all_chunkings(calibs, demo_pair, ctas_per_sm, bu
                 assert np.array_equal(tl[i], np.stack([lut[ch][wl[..., 2 - ch]] for ch in range(3)]))
 
 
+@pytest.mark.parametrize("n_handles,n", [(2, 9), (3, 10), (4, 3)])
+def test_run_batch_multi_equals_one_handle_bit_for_bit(calibs, demo_pair, n_handles, n):
+    """sa_run_batch_multi cuts a host batch frame-wise over several handles (one per GPU, one host thread each) and must give
+    exactly what sa_run_batch gives for the whole batch on one handle - point clouds, disparity (the stub numbers frames across
+    shards), rectified images, heat maps.  Handles go to distinct GPUs when the box has them, else they share GPU 0 (the
+    partition, the pointer arithmetic and the threading are the same).  (4, 3): more handles than pairs, one shard is empty."""
+    import torch
+    from stereoalgorithms_b200.geometry import PinnedArray, run_batch_multi
+    c = calibs["calib_b"]
+    W, H = 640, 480
+    rng = np.random.default_rng(77)
+    L = PinnedArray((n, H, W, 3), np.uint8)
+    R = PinnedArray((n, H, W, 3), np.uint8)
+    for i in range(n):
+        L.array[i] = np.roll(demo_pair[0], int(rng.integers(0, W)), axis=1)
+        R.array[i] = np.roll(demo_pair[1], int(rng.integers(0, W)), axis=1)
+    ngpu = torch.cuda.device_count()
+    per = -(-n // n_handles)
+
+    def outputs():
+        return dict(pointcloud=np.zeros((n, W * H, 6), np.float32), disparity=np.zeros((n, H, W), np.float32),
+                    rect_left=np.zeros((n, H, W, 3), np.uint8), rect_right=np.zeros((n, H, W, 3), np.uint8), heatmap=np.zeros((n, H, W, 3), np.uint8))
+
+    one, many = outputs(), outputs()
+    with geom(W, H, model="RAFTStereo", max_batch=n) as g:
+        g.set_calibration(c)
+        g.set_option("chunk", 4)
+        g.run_batch(L.array, R.array, n, rectify=True, stub_seed=99, **one)
+    gs = [geom(W, H, model="RAFTStereo", max_batch=per, gpu_id=i % ngpu) for i in range(n_handles)]
+    try:
+        for g in gs:
+            g.set_calibration(c)
+            g.set_option("chunk", 2)
+        for _ in range(2):                                    # twice: nothing of the first call may linger
+            run_batch_multi(gs, L.array, R.array, n, rectify=True, stub_seed=99, **many)
+        # too many pairs for the handles: a clear error, nothing crashes
+        from stereoalgorithms_b200.geometry import StereoGeomError
+        if n > n_handles:
+            with pytest.raises(StereoGeomError, match="max_batch"):
+                run_batch_multi(gs[:1], L.array, R.array, n, rectify=True, stub_seed=99, **outputs())
+    finally:
+        for g in gs:
+            g.close()
+    assert (one["disparity"] > 0).mean() > 0.9
+    for k in one:
+        assert np.array_equal(one[k], many[k], equal_nan=True), k
+    (l1, l2), _ = O.rectify_maps(c, (W, H))
+    assert np.array_equal(many["rect_left"][n - 1], OC.remap(L.array[n - 1], l1, l2))
+    want, _ = O.reproject_dense(O.FASTACVNET_PLUS, many["disparity"][n - 1], many["rect_left"][n - 1], c["Q"])
+    assert_close_points(many["pointcloud"][n - 1], want, "last frame of the last shard")
+
+
 def test_engine_callback_sits_between_the_two_halves(calibs, demo_pair):
     """sa_set_engine: the slot of context->enqueueV3(stream) (TRTFastACVNet_plus.cpp:152).  The callback gets the device
     tensors of its chunk and the disparity slot, on the library's stream; here it checks the tensors it is handed and

@@ -22,6 +22,21 @@ def test_shard_range_partitions_everything():
         shard_range(10, 2, 2)
 
 
+def test_library_partition_is_the_same_partition():
+    """sa_shard_range (what sa_run_batch_multi cuts a host batch with) and sharding.shard_range (what bench.py's ranks use)."""
+    import ctypes as C
+    from stereoalgorithms_b200 import _lib
+    lib = _lib.load()
+    b, e = C.c_int(), C.c_int()
+    for n in (0, 1, 7, 64, 256, 512, 513, 1024):
+        for world in (1, 2, 3, 4, 8):
+            for r in range(world):
+                assert lib.sa_shard_range(n, r, world, C.byref(b), C.byref(e)) == 0
+                assert (b.value, e.value) == shard_range(n, r, world)
+    assert lib.sa_shard_range(10, 2, 2, C.byref(b), C.byref(e)) == _lib.SA_ERR_INVALID_ARG
+    assert lib.sa_shard_range(10, 0, 0, C.byref(b), C.byref(e)) == _lib.SA_ERR_INVALID_ARG
+
+
 def _free_port():
     s = socket.socket()
     s.bind(("127.0.0.1", 0))

@@ -185,6 +185,10 @@ def test_numpy_and_c_restatements_agree(calibs, demo_pair, model):
         assert np.array_equal(t[:3], OC.preprocess_eye(model, rl)) and np.array_equal(t[3:], OC.preprocess_eye(model, rr))
     else:
         assert np.array_equal(t[0], OC.preprocess_eye(model, rl)) and np.array_equal(t[1], OC.preprocess_eye(model, rr))
+    # extension a10: the f16 flavour of the C restatement rounds exactly like numpy's astype(float16)
+    t16 = O.preprocess(model, rl, rr, np.float16)
+    h16 = OC.preprocess_eye(model, rl, np.float16)
+    assert h16.dtype == np.float16 and np.array_equal(h16, t16[:3] if model == O.HITNET else t16[0])
     d = O.synthetic_disparity(640, 480)
     if model == O.RAFTSTEREO:
         d = -d
