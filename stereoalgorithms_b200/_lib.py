@@ -6,7 +6,7 @@ import ctypes as C
 import os
 
 PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(PKG, "libstereo_geom.so")
+LIB_PATH = os.environ.get("SA_GEOM_LIB") or os.path.join(PKG, "libstereo_geom.so")   # the override is for tuning experiments (tools/)
 
 # enum mirrors of include/stereo_geom.h
 SA_OK = 0

@@ -49,5 +49,32 @@ def build(force: bool = False, verbose: bool = False) -> str:
     return LIB
 
 
+def build_variant(name: str, flags: list[str], sources=("rectify.cu",)) -> str:
+    """Tuning experiments: recompile `sources` with extra nvcc flags (e.g. -DSA_BATCH16_MINB_FIXED=4) and link them with the
+    regular objects into tools/exp/_bin/libstereo_geom_<name>.so; run with SA_GEOM_LIB=<that path>."""
+    build()
+    out_dir = os.path.join(os.path.dirname(PKG), "tools", "exp", "_bin")
+    os.makedirs(out_dir, exist_ok=True)
+    objs = []
+    for src in SOURCES:
+        if src in sources:
+            obj = os.path.join(out_dir, f"{name}_{src}.o")
+            r = subprocess.run(["nvcc", *NVCC_FLAGS, *flags, "-x", "cu", "-c", os.path.join(CSRC, src), "-o", obj], capture_output=True, text=True)
+            if r.returncode != 0:
+                raise RuntimeError(r.stderr)
+            with open(obj + ".ptxas.log", "w") as f:
+                f.write(r.stderr)
+            objs.append(obj)
+        else:
+            objs.append(os.path.join(OBJ, src + ".o"))
+    lib = os.path.join(out_dir, f"libstereo_geom_{name}.so")
+    subprocess.check_call(["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", lib, *objs, "-lcudart_static", "-lpthread", "-ldl", "-lrt"])
+    return lib
+
+
 if __name__ == "__main__":
+    if "--variant" in sys.argv:                               # python -m stereoalgorithms_b200.build --variant NAME FLAG...
+        i = sys.argv.index("--variant")
+        print(build_variant(sys.argv[i + 1], sys.argv[i + 2:]))
+        sys.exit(0)
     print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

@@ -200,6 +200,7 @@ static int stage_rectify(sa_handle* h, int f0, int n, const uint8_t* src_l, cons
         a.chunk_taper = (int)h->opt_chunk_taper;
         a.force_unaligned = (int)h->opt_force_unaligned;
         a.no_fixed_size = (int)h->opt_no_fixed_size;
+        a.no_align16 = (int)h->opt_no_align16;
         a.box_w = h->box_w; a.box_h = h->box_h;
         {
             StageScope t(h, SA_STAGE_RECTIFY, s);
@@ -1021,6 +1022,7 @@ int sa_set_option(sa_handle* h, const char* key, long value)
     else if (!std::strcmp(key, "scalar_preprocess")) h->opt_scalar_preprocess = value;
     else if (!std::strcmp(key, "l2_prefetch")) h->opt_l2_prefetch = value;
     else if (!std::strcmp(key, "frame_base")) h->opt_frame_base = value;
+    else if (!std::strcmp(key, "no_align16")) h->opt_no_align16 = value;
     else if (!std::strcmp(key, "chunk_taper")) h->opt_chunk_taper = value < 0 ? 0 : (value > 95 ? 95 : value);
     else return fail(h, SA_ERR_INVALID_ARG, "sa_set_option: unknown key '%s'", key);
     return SA_OK;

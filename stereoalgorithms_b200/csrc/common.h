@@ -112,6 +112,7 @@ struct sa_handle {
     long opt_l2_prefetch = -1;        // see RectifyArgs::l2_prefetch; -1 = automatic
     long opt_bulk = 0;                // rectify_tma_kernel when the frames are 16-byte aligned
     long opt_batch_loop = 1;          // rectify_batch_kernel (default); 0 = one CTA per (tile, eye, frame)
+    long opt_no_align16 = 0;          // 1 = keep the 4-byte-aligned frame loop even where the 16-byte one applies
     long opt_frame_base = 0;          // global index of this handle's frame 0 (sa_run_batch_multi: the stub numbers frames across shards)
     int sm_count = 148;
 
@@ -182,6 +183,7 @@ struct RectifyArgs {
     int l2_prefetch;                   // batch kernel: prefetch.global.L2 of the frame this many iterations ahead (0 = off, < 0 = automatic)
     int box_w, box_h;                  // largest staged footprint of the calibration over full tiles (pixels, rows), both eyes
     int batch_ctas_per_sm;             // target number of CTAs per SM for the frame chunking of the batch kernel
+    int no_align16;                    // batch kernel: do not take the 16-byte-aligned frame loop (tests, tuning)
 };
 cudaError_t launch_rectify(const RectifyArgs& a, cudaStream_t s, long* launches);
 

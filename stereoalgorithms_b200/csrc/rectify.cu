@@ -28,6 +28,8 @@
 //   preprocess4_kernel / preprocess_kernel   rectify = 0 and the tail of the resize path: normalise + planarise only
 #include <cuda.h>   // CUtensorMap and its enums only; the one driver function used is fetched with cudaGetDriverEntryPoint
 
+#include <type_traits>
+
 #include "common.h"
 
 #ifndef SA_BLEND_DP4A
@@ -46,6 +48,8 @@ __device__ __forceinline__ uint32_t fetch_px(const uint8_t* __restrict__ src, si
     }
     return 0u;
 }
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 template <typename V>
 __device__ __forceinline__ void copy_rows(uint8_t* __restrict__ g, size_t gpitch, const uint8_t* s, int rows, int row_bytes)
@@ -217,7 +221,16 @@ __device__ __forceinline__ void tile_fast(const RectifyArgs& a, const TileInfo t
 }
 
 // ---- generic path: partial tiles at the right/bottom edge, footprints too large to stage, odd alignments ---------
-template <int DTYPE, bool IDENT, bool WRITE_TENSOR, bool ALIGNED4>
+// CTA-wide barrier, or (NAMED) barrier 1 over the first kRectThreads threads only - the consumer threads of the warp-specialised
+// kernel, whose producer warps have left by then.
+template <bool NAMED>
+__device__ __forceinline__ void tile_sync()
+{
+    if (NAMED) asm volatile("bar.sync 1, %0;" ::"n"(kRectThreads) : "memory");
+    else __syncthreads();
+}
+
+template <int DTYPE, bool IDENT, bool WRITE_TENSOR, bool ALIGNED4, bool NAMED_BAR = false>
 __device__ __forceinline__ void tile_generic(const RectifyArgs& a, const TileInfo ti, int eye, int frame, int tx0, int ty0, int out_align,
                                              uint32_t* s_src, uint32_t* s_out, const typename TensorT<DTYPE>::type* s_lut)
 {
@@ -242,7 +255,7 @@ __device__ __forceinline__ void tile_generic(const RectifyArgs& a, const TileInf
             *reinterpret_cast<uint4*>(&s_src[g << 2]) = stage_checked<ALIGNED4>(src, pitch, W, H, X0 + c4, Y0 + r);
         }
     }
-    __syncthreads();
+    tile_sync<NAMED_BAR>();
 
     uint8_t* s_out_b = reinterpret_cast<uint8_t*>(s_out);
     const size_t plane = (size_t)W * H;
@@ -279,7 +292,7 @@ __device__ __forceinline__ void tile_generic(const RectifyArgs& a, const TileInf
             }
         }
     }
-    __syncthreads();
+    tile_sync<NAMED_BAR>();
 
     // rectified BGR tile -> global, widest stores the alignment allows
     const int rows = min(kTileH, H - ty0), row_bytes = min(kTileW, W - tx0) * 3;
@@ -674,46 +687,40 @@ __device__ __forceinline__ void rectify_batch_body(const RectifyArgs& a, int til
     }
 }
 
-template <int DTYPE, bool IDENT, bool WRITE_TENSOR, bool A4, int FW = 0, int FH = 0>
-// 5 CTAs per SM for the fixed-size identity-normalisation instantiations (RAFT / CRE): without the address arithmetic they
-// fit 48 registers without spilling (0.102 -> 0.099 ms); the LUT variants spill at 48 and lose 8 %, so they stay at 4.
-__global__ void __launch_bounds__(kRectThreads, (FW && IDENT) ? SA_BATCH_MINB_FIXED : SA_BATCH_MINB) rectify_batch_kernel(const RectifyArgs a, int tiles_x, int out_align, int frames_per_cta)
-{
-    using T = typename TensorT<DTYPE>::type;
-    __shared__ __align__(16) uint32_t s_src2[2][kFootprintWords];   // double buffered: one barrier per frame
-    __shared__ T s_lut[IDENT ? 1 : 768];
-    if (!IDENT) {
-        const T* lut = static_cast<const T*>(a.lut);
-        for (int i = threadIdx.x; i < 768; i += kRectThreads) s_lut[i] = lut[i];
-    }
-    if (FW) {                                                        // fixed sizes are multiples of the tile: no partial tiles
-        static_assert(FW % kTileW == 0 && FH % kTileH == 0, "fixed-size instantiation needs whole tiles");
-        rectify_batch_body<DTYPE, IDENT, WRITE_TENSOR, A4, false, FW, FH>(a, tiles_x, out_align, frames_per_cta, s_src2, s_lut);
-        return;
-    }
-    const bool full = (int)(blockIdx.x + 1) * kTileW <= a.W && (int)(blockIdx.y + 1) * kTileH <= a.H;
-    if (full) rectify_batch_body<DTYPE, IDENT, WRITE_TENSOR, A4, false>(a, tiles_x, out_align, frames_per_cta, s_src2, s_lut);
-    else rectify_batch_body<DTYPE, IDENT, WRITE_TENSOR, A4, true>(a, tiles_x, out_align, frames_per_cta, s_src2, s_lut);
-}
+// ---- warp-specialised flavour of the batch loop (default for 16-byte-aligned input) --------------------------------------------
+// Same work decomposition as rectify_batch_kernel - one CTA per (tile, eye) walks a run of frames - but the two halves of a
+// frame's work no longer share the threads or a CTA-wide barrier:
+//   * 2 PRODUCER warps stage the footprints: a staging unit is 16 source pixels = 48 bytes = three 16-byte loads by one lane,
+//     expanded to sixteen BGRx words and stored as four 16-byte shared-memory stores.  A footprint has at most 6 x 32 units
+//     (typically ~100), so a lane owns two, rarely three.  They fill a ring of three BGRx stages, run up to two frames
+//     ahead of the blend, and pull the frame after that into L2 (two prefetches per unit: a 48-byte unit lies in exactly two
+//     32-byte sectors).  Their load latency is exposed only to themselves.
+//   * 8 CONSUMER warps (256 threads, the pixel mapping of the kernel above) do nothing but blend and store: they wait on the
+//     stage's "full" mbarrier, read their taps with LDS [reg + imm] (the staged rows have a compile-time stride), and release the
+//     stage with one "empty" arrive per warp.  No __syncthreads, no loads, no staging arithmetic in their loop.
+// In the kernel above every thread does both jobs and every frame ends at a barrier the slowest warp decides; ncu shows it
+// issue-/latency-bound (issue slots 71 % busy, 1.5 warps per issue stalled at the barrier, 2.1 on the loads' scoreboard) with 83 of
+// 231 instructions per thread and frame spent on staging and bookkeeping (profiles/r02_stage_a.md).
+// Other changes that ride along:
+//   * staged row stride 100 words and units assigned to lanes column-major: the eight lanes of a quarter-warp store to eight
+//     different 16-byte bank groups (a 96-word stride with row-major units gave 4-way conflicts on every store);
+//   * units that lie outside the image are zeroed once in all stages, not re-stored every frame;
+//   * RAFT / CRE f16 tensors: the vertical dot product starts from 512 + (0x6400 << 10), so that after the shift the low 16 bits
+//     are the half-precision bit pattern of 1024 + v; one half subtraction gives (half)v - no integer-to-float conversion
+//     (I2F.F16 issues at a quarter of the ALU rate).
+// Needs: image rows, frames and bases 16-byte aligned, W % 16 == 0 (a unit is then all inside or all outside the image), and
+// every footprint of the calibration at most 96 pixels wide and 32 rows high (launch_rectify_t checks the calibration's largest
+// footprint; a single larger tile falls back to the bounds-checked path).
+constexpr int kWsStride = 100;                          // words per staged footprint row
+constexpr int kWsStrideB = kWsStride * 4;
+constexpr int kWsMaxW = 96, kWsMaxH = 32;               // largest footprint (pixels, rows)
+constexpr int kWsStageWords = kWsStride * kWsMaxH;      // 12.8 KB per stage
+constexpr int kWsStageB = kWsStageWords * 4;
+constexpr int kWsStages = 2;                            // BGRx stages: one being blended, one being filled
+constexpr int kWsRawStages = 3;                         // raw (packed BGR) stages: two tensor copies in flight while one is expanded
+constexpr int kWsProducers = 128;                       // four warps = one warpgroup (setmaxnreg works on whole warpgroups)
+constexpr int kWsThreads = kRectThreads + kWsProducers;
 
-// ---- TMA variant: the footprint arrives as ONE tensor copy per frame, an mbarrier ring orders producer and consumers ------
-// Same work decomposition as rectify_batch_kernel (one CTA per (tile, eye), a run of frames), but the staging is done by
-// the Tensor Memory Accelerator: the source batch is described once per launch by a 3-D tensor map over 4-byte words
-// (3W/4 words x H rows x n frames, byte strides = row pitch and frame size), and for every frame ONE elected thread issues
-// ONE cp.async.bulk.tensor.3d for a box of (bw words x bh rows x 1 frame) at the tile's footprint origin, completing on an
-// mbarrier.  The box is the largest footprint of the calibration; whatever part of it lies outside the image - negative
-// coordinates included - is zero-filled by the hardware, which is exactly BORDER_CONSTANT 0.  Three raw (packed BGR)
-// stages are in flight: frames f+1 and f+2 travel while frame f is blended.  No thread spends instructions or registers
-// on loads, there is no __syncthreads in the frame loop (warps wait on / arrive at the mbarriers of the ring), and the
-// taps are read straight from the packed rows: three aligned words per row and two funnel shifts give the six bytes of a
-// horizontal tap pair at any byte offset.
-// Requirements on top of A4: source base, row pitch and frame size multiples of 16 bytes.
-// (Bulk and tensor copies need a 16-byte aligned global start; a footprint origin is only a multiple of 4 pixels = 12 bytes,
-// so the box starts at the origin rounded down to 16 pixels.  tools/exp/tma_test.cu is the micro-test that pinned this down.)
-constexpr int kTmaStages = 3;
-constexpr int kTmaStageBytes = 12288;
-
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count)
 {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
@@ -738,136 +745,267 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
         "DONE_%=:\n"
         "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
 }
+
+// 12 source bytes -> four BGRx words (byte 3 of a staged word is never read), one 16-byte shared-memory store
+__device__ __forceinline__ void put4(uint32_t addr, uint32_t w0, uint32_t w1, uint32_t w2)
+{
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(w0), "r"(__byte_perm(w0, w1, 0x4543)), "r"(__byte_perm(w1, w2, 0x4432)), "r"(w2 >> 8)
+                 : "memory");
+}
+__device__ __forceinline__ void put_unit(uint32_t addr, const uint4& u0, const uint4& u1, const uint4& u2)
+{
+    put4(addr, u0.x, u0.y, u0.z);
+    put4(addr + 16u, u0.w, u1.x, u1.y);
+    put4(addr + 32u, u1.z, u1.w, u2.x);
+    put4(addr + 48u, u2.y, u2.z, u2.w);
+}
+
 __device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* tm, int c0, int c1, int c2, uint64_t* bar)
 {
     asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(smem_u32(dst)),
                  "l"(tm), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(bar))
                  : "memory");
 }
+__device__ __forceinline__ void tma_prefetch_3d(const CUtensorMap* tm, int c0, int c1, int c2)
+{
+    asm volatile("cp.async.bulk.prefetch.tensor.3d.L2.global.tile [%0, {%1, %2, %3}];" ::"l"(tm), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
 
-#ifndef SA_TMA_MINB
-#define SA_TMA_MINB 4
-#endif
-template <int DTYPE, bool IDENT, bool WRITE_TENSOR>
-__global__ void __launch_bounds__(kRectThreads, SA_TMA_MINB)
-    rectify_tma_kernel(const RectifyArgs a, const __grid_constant__ CUtensorMap tm_left, const __grid_constant__ CUtensorMap tm_right, int tiles_x, int out_align,
-                       int frames_per_cta, int bw, int bh)
+// Producer warps: bring frames [f0, f1) of one (tile, eye) into the BGRx ring.
+// The packed source bytes of a frame's footprint arrive as ONE tensor copy (cp.async.bulk.tensor.3d: box = the largest footprint of
+// the calibration, bw words x bh rows x 1 frame of a 3-D map over 4-byte words; whatever lies outside the image - negative
+// coordinates included - is zero-filled by the copy engine, which is BORDER_CONSTANT 0) into one of two raw stages, completing
+// on that stage's mbarrier; the copy of frame f+1 is in flight while frame f is expanded, and frame f+3 is pulled into L2 by a
+// tensor prefetch.  No thread spends an instruction on global addresses, bounds or load latency.  The 64 producer lanes then
+// expand the box, 16 pixels (three 16-byte shared loads -> four 16-byte shared stores) per lane and round, into the BGRx stage
+// the consumers read.
+__device__ __forceinline__ void ws_produce(const TileInfo ti, const CUtensorMap* tm, int bw, int bh, int f0, int f1, int pfd, uint32_t raw0, uint32_t raw_stage_b,
+                                           uint32_t stage0, uint32_t stage_b, uint64_t* s_rawfull, uint64_t* s_full, uint64_t* s_empty)
+{
+    const int p = threadIdx.x - kRectThreads;                          // 0..127
+    const int cx = 3 * (ti.x0 >> 2), cy = ti.y0;                       // box origin: word column (x0 is a multiple of 16 pixels = 12 words), row
+    const uint32_t rowb = (uint32_t)bw * 4u, box_bytes = rowb * (uint32_t)bh;
+    const int nunits = (bw / 12) * bh;                                 // 16-pixel units in the box
+    if (p == 0) {
+#pragma unroll
+        for (int j = 0; j < kWsRawStages; j++)
+            if (f0 + j < f1) {
+                mbar_expect_tx(&s_rawfull[j], box_bytes);
+                tma_load_3d(reinterpret_cast<void*>(__cvta_shared_to_generic(raw0 + j * raw_stage_b)), tm, cx, cy, f0 + j, &s_rawfull[j]);
+            }
+        for (int j = kWsRawStages; j < kWsRawStages + pfd; j++)
+            if (f0 + j < f1) tma_prefetch_3d(tm, cx, cy, f0 + j);
+    }
+    // this lane's units (at most two: a box has at most 192): byte offset inside a raw stage / inside a BGRx stage
+    uint32_t uraw[2], udst[2];
+#pragma unroll
+    for (int j = 0; j < 2; j++) {
+        const int u = p + j * kWsProducers;
+        const int c = u / bh, r = u - c * bh;                          // column-major: the lanes of a quarter-warp hit different bank groups
+        uraw[j] = u < nunits ? (uint32_t)r * rowb + 48u * (uint32_t)c : 0xffffffffu;       // 0xffffffff = none
+        udst[j] = (uint32_t)(r * kWsStride + 16 * c) * 4u;
+    }
+    const bool second = nunits > kWsProducers;                         // CTA-uniform: most boxes need one unit per lane
+    auto expand = [](uint32_t ra, uint32_t da) {                       // 48 packed bytes -> sixteen BGRx words
+        uint4 u0, u1, u2;
+        asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(u0.x), "=r"(u0.y), "=r"(u0.z), "=r"(u0.w) : "r"(ra));
+        asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4+16];" : "=r"(u1.x), "=r"(u1.y), "=r"(u1.z), "=r"(u1.w) : "r"(ra));
+        asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4+32];" : "=r"(u2.x), "=r"(u2.y), "=r"(u2.z), "=r"(u2.w) : "r"(ra));
+        put_unit(da, u0, u1, u2);
+    };
+    uint32_t rs = 0, rround = 0;                                       // raw ring position
+    for (int f = f0; f < f1; f++) {
+        const uint32_t i = (uint32_t)(f - f0), st = i & 1u, round = i >> 1;
+        mbar_wait(&s_rawfull[rs], rround & 1u);                         // the packed bytes of frame f have landed
+        if (round) mbar_wait(&s_empty[st], (round - 1) & 1u);          // the consumers are done with the BGRx stage's previous frame
+        const uint32_t rsrc = raw0 + rs * raw_stage_b, rdst = stage0 + st * stage_b;
+        if (uraw[0] != 0xffffffffu) expand(rsrc + uraw[0], rdst + udst[0]);
+        if (second && uraw[1] != 0xffffffffu) expand(rsrc + uraw[1], rdst + udst[1]);
+        mbar_arrive(&s_full[st]);                                       // release: this lane's stores are visible to whoever acquires the barrier
+        // the raw stage is free once both producer warps have read it: refill it with frame f + kWsRawStages
+        asm volatile("bar.sync 2, %0;" ::"n"(kWsProducers) : "memory");
+        if (p == 0) {
+            if (f + kWsRawStages < f1) {
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy reads of the stage before the async-proxy write
+                mbar_expect_tx(&s_rawfull[rs], box_bytes);
+                tma_load_3d(reinterpret_cast<void*>(__cvta_shared_to_generic(rsrc)), tm, cx, cy, f + kWsRawStages, &s_rawfull[rs]);
+            }
+            if (pfd && f + kWsRawStages + pfd < f1) tma_prefetch_3d(tm, cx, cy, f + kWsRawStages + pfd);
+        }
+        if (++rs == kWsRawStages) { rs = 0; ++rround; }
+    }
+}
+
+// Consumer warps: blend frames [f0, f1) of one (tile, eye) out of the ring and store rectified bytes + tensors.
+template <int DTYPE, bool IDENT, bool WRITE_TENSOR, bool PART, int FW, int FH>
+__device__ __forceinline__ void ws_consume(const RectifyArgs& a, const TileInfo ti, int eye, int W, int H, int f0, int f1, int tx0, int ty0, uint32_t stage0,
+                                           uint32_t stage_b, uint64_t* s_full, uint64_t* s_empty, const typename TensorT<DTYPE>::type* s_lut)
 {
     using T = typename TensorT<DTYPE>::type;
-    __shared__ __align__(128) uint32_t s_raw[kTmaStages][kTmaStageBytes / 4];   // packed BGR boxes, bw words per row
-    __shared__ __align__(8) uint64_t s_full[kTmaStages], s_empty[kTmaStages];
-    __shared__ T s_lut[IDENT ? 1 : 768];
-
-    const int tid = threadIdx.x, lane = tid & 31;
-    const int W = a.W, H = a.H;
-    const int eye = blockIdx.z & 1, chunk = blockIdx.z >> 1;
-    const int f0 = chunk * frames_per_cta, f1 = min(a.n, f0 + frames_per_cta);
-    const int tx0 = blockIdx.x * kTileW, ty0 = blockIdx.y * kTileH;
-    const TileInfo ti = a.tiles[eye][blockIdx.y * tiles_x + blockIdx.x];
-    if (!IDENT) {
-        const T* lut = static_cast<const T*>(a.lut);
-        for (int i = tid; i < 768; i += kRectThreads) s_lut[i] = lut[i];
+    constexpr bool HBIAS = IDENT && WRITE_TENSOR && DTYPE == SA_F16;   // blend results carry the 0x6400 half-precision bias
+    const int tid = threadIdx.x;
+    const int lx = tid & (kTileW - 1), ly = tid >> 6;
+    const int pix0 = (ty0 + ly) * W + tx0 + lx;
+    const int rstep = 4 * W, plane = W * H;
+    const size_t rect_pitch = FW ? (size_t)3 * FW : a.rect_pitch, rect_frame = FW ? (size_t)3 * FW * FH : a.rect_frame;
+    const int wstep = (int)rect_pitch;                                // words per 4 rows of the rectified image
+    uint32_t pvalid = 0xfu;                                           // bit k: pixel k of this thread lies inside the image
+    if (PART) {
+        pvalid = 0;
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+            if (tx0 + lx < W && ty0 + ly + 4 * k < H) pvalid |= 1u << k;
     }
-    const int rowb = bw * 4;                                             // bytes per row of a staged box
-    // the box must cover the footprint (+ the third word every tap pair reads); it does for every staged full tile
-    // The innermost coordinate of a tensor copy must be a multiple of 16 bytes: the box starts at the footprint origin
-    // rounded down to 16 pixels (48 bytes), xpad pixels left of it.
-    const int xpad = ti.x0 & 15;
-    const bool fast = ti.w > 0 && tx0 + kTileW <= W && ty0 + kTileH <= H && 3 * (ti.w + xpad) + 8 <= rowb && ti.h <= bh;
-    if (!fast) {   // edge tile / unstaged or oversized footprint: generic path, frame by frame (s_raw doubles as its scratch)
-        for (int f = f0; f < f1; f++) {
-            __syncthreads();
-            tile_generic<DTYPE, IDENT, WRITE_TENSOR, true>(a, ti, eye, f, tx0, ty0, out_align, s_raw[0], s_raw[1], s_lut);
-        }
-        return;
-    }
-    if (tid == 0) {
-        for (int st = 0; st < kTmaStages; st++) { mbar_init(&s_full[st], 1); mbar_init(&s_empty[st], kRectThreads / 32); }
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    __syncthreads();
-
-    const int pix0 = (ty0 + (tid >> 6)) * W + tx0 + (tid & (kTileW - 1));
-    const int rstep = 4 * W, wstep = 3 * W, plane = W * H;
-    uint32_t toff[4], twt[4];           // byte offset of the top-left tap pair inside a staged box (low 2 bits = byte shift); weights
+    uint32_t toff[4], twt[4];           // shared-memory byte address of the top-left tap in stage 0; (32-fx, fx, 32-fy, fy) as four bytes
     {
         const uint32_t* __restrict__ tmap = a.tmap[eye] + pix0;
         const uint32_t fw = (uint32_t)ti.w;
 #pragma unroll
         for (int k = 0; k < 4; k++) {
-            const uint32_t t = __ldg(tmap + k * rstep);
+            const uint32_t t = (!PART || ((pvalid >> k) & 1u)) ? __ldg(tmap + k * rstep) : 0u;
             const uint32_t fx = (t >> 12) & 31u, fy = (t >> 17) & 31u, off = t & 0xfffu;
-            const uint32_t ry = off / fw, rx = off - ry * fw;
-            toff[k] = ry * (uint32_t)rowb + 3u * (rx + (uint32_t)xpad);
+            const uint32_t ry = off / fw, rx = off - ry * fw;            // the table is laid out with the tile's own row length
+            toff[k] = stage0 + (ry * kWsStride + rx) * 4u;
             twt[k] = (32u - fx) | (fx << 8) | ((32u - fy) << 16) | (fy << 24);
         }
     }
-    const CUtensorMap* tm = eye ? &tm_right : &tm_left;
-    const int cx = 3 * ((ti.x0 - xpad) >> 2), cy = ti.y0;                 // box origin: word column (a multiple of 12 words = 48 bytes), row
-    const uint32_t stage_tx = (uint32_t)(rowb * bh);
     const int m = tid & 3;
     uint32_t sel = m == 0 ? 0x4210u : (m == 1 ? 0x5421u : 0x6542u);
-    asm volatile("" : "+r"(sel));
-    uint32_t* __restrict__ rp = rect_words(a.rect[eye] + (size_t)f0 * a.rect_frame, a.rect_pitch, ty0 + (tid >> 6), tx0 + (tid & (kTileW - 1)), m);
+    asm volatile("" : "+r"(sel));       // keep it in a register: recomputing the selects inside the frame loop costs 5 instructions per pixel
+    uint32_t* __restrict__ rp = rect_words(a.rect[eye] + (size_t)f0 * rect_frame, rect_pitch, ty0 + ly, tx0 + lx, m);
     T* __restrict__ tp = WRITE_TENSOR ? static_cast<T*>(a.tensor[eye]) + (size_t)f0 * a.tensor_frame + pix0 : nullptr;
-    const size_t rect_frame_words = a.rect_frame / 4;
-    const int nf = f1 - f0;
-    const int roww = bw;                                                // words per staged row
+    const size_t rect_frame_words = rect_frame / 4;
+    constexpr uint32_t kAcc = HBIAS ? (512u + (0x6400u << 10)) : 512u;
+    const int lane = tid & 31;
 
-    if (tid == 0) {
-        mbar_expect_tx(&s_full[0], stage_tx);
-        tma_load_3d(s_raw[0], tm, cx, cy, f0, &s_full[0]);
-        if (nf > 1) {
-            mbar_expect_tx(&s_full[1], stage_tx);
-            tma_load_3d(s_raw[1], tm, cx, cy, f0 + 1, &s_full[1]);
-        }
-    }
-    for (int i = 0; i < nf; i++) {
-        const int st = i % kTmaStages;
-        // refill the stage that was consumed in the previous iteration with frame i + 2
-        if (tid == 0 && i + 2 < nf) {
-            const int st2 = (i + 2) % kTmaStages;
-            if (i >= 1) mbar_wait(&s_empty[st2], (uint32_t)(((i - 1) / kTmaStages) & 1));
-            mbar_expect_tx(&s_full[st2], stage_tx);
-            tma_load_3d(s_raw[st2], tm, cx, cy, f0 + i + 2, &s_full[st2]);
-        }
-        __syncwarp();
-        mbar_wait(&s_full[st], (uint32_t)((i / kTmaStages) & 1));
-
-        const uint32_t* sw = s_raw[st];
+    uint32_t st = 0, round = 0, so = 0;
+    for (int f = f0; f < f1; f++) {
+        mbar_wait(&s_full[st], round & 1u);
 #pragma unroll
         for (int k = 0; k < 4; k++) {
-            const uint32_t sh = (toff[k] & 3u) << 3;
-            const uint32_t* p = sw + (toff[k] >> 2);
-            const uint32_t* q = p + roww;
-            const uint32_t a0 = p[0], a1 = p[1], a2 = p[2];
-            const uint32_t b0 = q[0], b1 = q[1], b2 = q[2];
-            // six bytes of the tap pair: lo = B0 G0 R0 B1, hi = G1 R1 . .
-            const uint32_t tlo = __funnelshift_r(a0, a1, sh), thi = __funnelshift_r(a1, a2, sh);
-            const uint32_t blo = __funnelshift_r(b0, b1, sh), bhi = __funnelshift_r(b1, b2, sh);
+            uint32_t p00, p01, p10, p11;
+            const uint32_t ad = toff[k] + so;
+            asm volatile("ld.shared.b32 %0, [%1];" : "=r"(p00) : "r"(ad));
+            asm volatile("ld.shared.b32 %0, [%1+4];" : "=r"(p01) : "r"(ad));
+            asm volatile("ld.shared.b32 %0, [%1+%2];" : "=r"(p10) : "r"(ad), "n"(kWsStrideB));
+            asm volatile("ld.shared.b32 %0, [%1+%2];" : "=r"(p11) : "r"(ad), "n"(kWsStrideB + 4));
             const uint32_t wt = twt[k];
             const uint32_t wx = wt & 0xffffu, wxh = wt << 16;
-            const uint32_t tBG = __byte_perm(tlo, thi, 0x4130), tRR = __byte_perm(tlo, thi, 0x5252);
-            const uint32_t bBG = __byte_perm(blo, bhi, 0x4130), bRR = __byte_perm(blo, bhi, 0x5252);
+            const uint32_t tBG = __byte_perm(p00, p01, 0x5140), tRR = __byte_perm(p00, p01, 0x6262);
+            const uint32_t bBG = __byte_perm(p10, p11, 0x5140), bRR = __byte_perm(p10, p11, 0x6262);
             const uint32_t tB = __dp4a(tBG, wx, 0u), tG = __dp4a(tBG, wxh, 0u), tR = __dp4a(tRR, wx, 0u);
             const uint32_t bB = __dp4a(bBG, wx, 0u), bG = __dp4a(bBG, wxh, 0u), bR = __dp4a(bRR, wx, 0u);
-            const uint32_t vB = __dp2a_hi(__byte_perm(tB, bB, 0x5410), wt, 512u) >> 10;
-            const uint32_t vG = __dp2a_hi(__byte_perm(tG, bG, 0x5410), wt, 512u) >> 10;
-            const uint32_t vR = __dp2a_hi(__byte_perm(tR, bR, 0x5410), wt, 512u) >> 10;
-            const uint32_t v = vB | (vG << 8) | (vR << 16);
-            const uint32_t nb = __shfl_down_sync(0xffffffffu, v, 1);
-            if (m < 3) rp[k * wstep] = __byte_perm(v, nb, sel);
-            if (WRITE_TENSOR) {
+            // vertical pass: (t, b) as two 16-bit lanes . (32-fy, fy) = bytes 2,3 of wt, plus the rounding constant (and the half bias)
+            const uint32_t vB = __dp2a_hi(__byte_perm(tB, bB, 0x5410), wt, kAcc) >> 10;
+            const uint32_t vG = __dp2a_hi(__byte_perm(tG, bG, 0x5410), wt, kAcc) >> 10;
+            const uint32_t vR = __dp2a_hi(__byte_perm(tR, bR, 0x5410), wt, kAcc) >> 10;
+            const bool pv = !PART || ((pvalid >> k) & 1u);
+            {
+                // B | G << 8 | R << 16 from the low bytes (with the half bias the upper bytes are not clean)
+                const uint32_t v = HBIAS ? __byte_perm(__byte_perm(vB, vG, 0x7740), vR, 0x7410) : (vB | (vG << 8) | (vR << 16));
+                const uint32_t nb = __shfl_down_sync(0xffffffffu, v, 1);
+                if (m < 3 && pv) rp[k * wstep] = __byte_perm(v, nb, sel);
+            }
+            if (WRITE_TENSOR && pv) {
                 T r, g, b;
-                normalise<DTYPE, IDENT, T>(s_lut, vB, vG, vR, r, g, b);
+                if (HBIAS) {
+                    const __half k1024 = __ushort_as_half((unsigned short)0x6400);
+                    r = (T)__hsub(__ushort_as_half((unsigned short)vR), k1024);
+                    g = (T)__hsub(__ushort_as_half((unsigned short)vG), k1024);
+                    b = (T)__hsub(__ushort_as_half((unsigned short)vB), k1024);
+                } else {
+                    normalise<DTYPE, IDENT, T>(s_lut, vB, vG, vR, r, g, b);
+                }
                 tp[k * rstep] = r; tp[k * rstep + plane] = g; tp[k * rstep + 2 * plane] = b;
             }
         }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&s_empty[st]);                       // this warp has read everything it needs from the stage
         rp += rect_frame_words;
         if (WRITE_TENSOR) tp += a.tensor_frame;
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&s_empty[st]);                       // this warp is done reading the stage
+        so += stage_b;
+        if (++st == kWsStages) { st = 0; so = 0; ++round; }
     }
+}
+
+#ifndef SA_WS_MINB
+#define SA_WS_MINB 4
+#endif
+template <int DTYPE, bool IDENT, bool WRITE_TENSOR, int FW = 0, int FH = 0>
+__global__ void __launch_bounds__(kWsThreads, SA_WS_MINB)
+    rectify_ws_kernel(const RectifyArgs a, const __grid_constant__ CUtensorMap tm_left, const __grid_constant__ CUtensorMap tm_right, int tiles_x, int out_align,
+                      int frames_per_cta, int bw, int bh)
+{
+    using T = typename TensorT<DTYPE>::type;
+    // dynamic shared memory, sized by the calibration's largest footprint (launch_rectify_t): kWsRawStages raw boxes of
+    // raw_b bytes (bw words x bh rows, rounded up to 128), then kWsStages BGRx stages of stage_b bytes (bh rows of kWsStride words)
+    extern __shared__ __align__(128) uint8_t s_dyn[];
+    __shared__ __align__(8) uint64_t s_rawfull[kWsRawStages], s_full[kWsStages], s_empty[kWsStages];
+    __shared__ T s_lut[IDENT ? 1 : 768];
+    const uint32_t raw_b = ((uint32_t)(bw * 4 * bh) + 127u) & ~127u, stage_b = (uint32_t)(kWsStrideB * bh);
+    const int tid = threadIdx.x;
+    if (!IDENT) {
+        const T* lut = static_cast<const T*>(a.lut);
+        for (int i = tid; i < 768; i += kWsThreads) s_lut[i] = lut[i];
+    }
+    const int W = FW ? FW : a.W, H = FH ? FH : a.H;
+    const int eye = blockIdx.z & 1, chunk = blockIdx.z >> 1;
+    const int f0 = a.chunk_tab ? a.chunk_begin[chunk] : chunk * frames_per_cta;
+    const int f1 = a.chunk_tab ? a.chunk_begin[chunk + 1] : min(a.n, f0 + frames_per_cta);
+    const int tx0 = blockIdx.x * kTileW, ty0 = blockIdx.y * kTileH;
+    const TileInfo ti = a.tiles[eye][blockIdx.y * tiles_x + blockIdx.x];
+    if (tid == 0) {
+        for (int st = 0; st < kWsStages; st++) { mbar_init(&s_full[st], kWsProducers); mbar_init(&s_empty[st], kRectThreads / 32); }
+        for (int st = 0; st < kWsRawStages; st++) mbar_init(&s_rawfull[st], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();                                                    // barriers initialised, LUT in place; the only CTA-wide barrier
+    const bool staged = ti.w > 0 && ti.w * 3 <= bw * 4 && ti.h <= bh;    // the footprint lies inside the box of the tensor copies
+    if (!staged) {       // unstaged / oversized footprint: bounds-checked path, frame by frame, on the 256 consumer threads
+        if (tid >= kRectThreads) return;
+        for (int f = f0; f < f1; f++) {
+            tile_sync<true>();
+            tile_generic<DTYPE, IDENT, WRITE_TENSOR, true, true>(a, ti, eye, f, tx0, ty0, out_align, reinterpret_cast<uint32_t*>(s_dyn),
+                                                                 reinterpret_cast<uint32_t*>(s_dyn) + kFootprintWords, s_lut);   // (the launch reserves at least this much)
+        }
+        return;
+    }
+    const uint32_t raw0 = smem_u32(s_dyn), stage0 = raw0 + kWsRawStages * raw_b;
+    // Register split: the kernel is launched with 40 registers per thread (4 CTAs of 384 threads per SM); the producer
+    // warpgroup gives back down to 24 - it holds one 48-byte unit and a few addresses - and the two consumer warpgroups take
+    // 48 each: 128 x 24 + 256 x 48 = 384 x 40.
+    if (tid >= kRectThreads) {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 24;");
+        ws_produce(ti, eye ? &tm_right : &tm_left, bw, bh, f0, f1, a.l2_prefetch >= 0 ? a.l2_prefetch : 2, raw0, raw_b, stage0, stage_b, s_rawfull, s_full, s_empty);
+        return;
+    }
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 48;");
+    constexpr bool whole = FW && FW % kTileW == 0 && FH % kTileH == 0;   // no partial tiles at all
+    const bool full = whole || (tx0 + kTileW <= W && ty0 + kTileH <= H);
+    if (full) ws_consume<DTYPE, IDENT, WRITE_TENSOR, false, FW, FH>(a, ti, eye, W, H, f0, f1, tx0, ty0, stage0, stage_b, s_full, s_empty, s_lut);
+    else ws_consume<DTYPE, IDENT, WRITE_TENSOR, true, FW, FH>(a, ti, eye, W, H, f0, f1, tx0, ty0, stage0, stage_b, s_full, s_empty, s_lut);
+}
+
+template <int DTYPE, bool IDENT, bool WRITE_TENSOR, bool A4, int FW = 0, int FH = 0>
+// 5 CTAs per SM for the fixed-size identity-normalisation instantiations (RAFT / CRE): without the address arithmetic they
+// fit 48 registers without spilling (0.102 -> 0.099 ms); the LUT variants spill at 48 and lose 8 %, so they stay at 4.
+__global__ void __launch_bounds__(kRectThreads, (FW && IDENT) ? SA_BATCH_MINB_FIXED : SA_BATCH_MINB) rectify_batch_kernel(const RectifyArgs a, int tiles_x, int out_align, int frames_per_cta)
+{
+    using T = typename TensorT<DTYPE>::type;
+    __shared__ __align__(16) uint32_t s_src2[2][kFootprintWords];   // double buffered: one barrier per frame
+    __shared__ T s_lut[IDENT ? 1 : 768];
+    if (!IDENT) {
+        const T* lut = static_cast<const T*>(a.lut);
+        for (int i = threadIdx.x; i < 768; i += kRectThreads) s_lut[i] = lut[i];
+    }
+    if (FW) {                                                        // fixed sizes are multiples of the tile: no partial tiles
+        static_assert(FW % kTileW == 0 && FH % kTileH == 0, "fixed-size instantiation needs whole tiles");
+        rectify_batch_body<DTYPE, IDENT, WRITE_TENSOR, A4, false, FW, FH>(a, tiles_x, out_align, frames_per_cta, s_src2, s_lut);
+        return;
+    }
+    const bool full = (int)(blockIdx.x + 1) * kTileW <= a.W && (int)(blockIdx.y + 1) * kTileH <= a.H;
+    if (full) rectify_batch_body<DTYPE, IDENT, WRITE_TENSOR, A4, false>(a, tiles_x, out_align, frames_per_cta, s_src2, s_lut);
+    else rectify_batch_body<DTYPE, IDENT, WRITE_TENSOR, A4, true>(a, tiles_x, out_align, frames_per_cta, s_src2, s_lut);
 }
 
 // Encodes the 3-D tensor map of one eye's source batch.  The driver entry point is looked up once (no link-time libcuda).
@@ -1100,16 +1238,28 @@ cudaError_t launch_rectify_t(const RectifyArgs& a, bool aligned4, int tiles_x, i
         }
         if (2 * chunks <= 65535) {
             const dim3 g((unsigned)tiles_x, (unsigned)tiles_y, 2u * (unsigned)chunks);
-            // TMA staging: box = largest footprint of the calibration + up to 12 pixels of origin alignment, rows padded to 16 bytes
-            // plus the word the last tap pair over-reads
-            const int bw = ((3 * (a.box_w + 12) + 8 + 15) / 16) * 4, bh = a.box_h;
-            const bool tma_ok = a4 && a.bulk_copy && a.box_w > 0 && bw <= 256 && bh <= 256 && bw * 4 * bh <= kTmaStageBytes && a.src_pitch % 16 == 0 &&
-                                a.src_frame % 16 == 0 && ((uintptr_t)a.src[0] | (uintptr_t)a.src[1]) % 16 == 0;
-            if (tma_ok) {
+            // 16-byte-aligned input and footprints that fit a ring stage: the warp-specialised kernel
+            const bool a16 = a4 && !a.no_align16 && a.W % 16 == 0 && a.src_pitch % 16 == 0 && a.src_frame % 16 == 0 && ((uintptr_t)a.src[0] | (uintptr_t)a.src[1]) % 16 == 0 &&
+                             a.box_w > 0 && a.box_w <= kWsMaxW && a.box_h <= kWsMaxH;
+            if (a16) {
+                // box of the tensor copies = the largest footprint of the calibration (a multiple of 16 pixels wide), in 4-byte words
+                const int bw = a.box_w * 3 / 4, bh = a.box_h;
                 CUtensorMap tl, tr;
                 if (encode_source_map(&tl, a.src[0], a.W, a.H, a.n, a.src_pitch, a.src_frame, bw, bh) &&
                     encode_source_map(&tr, a.src[1], a.W, a.H, a.n, a.src_pitch, a.src_frame, bw, bh)) {
-                    rectify_tma_kernel<DTYPE, IDENT, WT><<<g, kRectThreads, 0, s>>>(a, tl, tr, tiles_x, out_align, fpc, bw, bh);
+                    size_t dyn = (size_t)kWsRawStages * (((size_t)bw * 4 * bh + 127) & ~(size_t)127) + (size_t)kWsStages * kWsStrideB * bh;
+                    const size_t generic_need = (size_t)(kFootprintWords + kTileH * kTileW * 3 / 4) * 4;   // scratch of the bounds-checked path
+                    if (dyn < generic_need) dyn = generic_need;
+#define SA_WS_LAUNCH(FWV, FHV)                                                                                                      \
+    do {                                                                                                                            \
+        auto kern = rectify_ws_kernel<DTYPE, IDENT, WT, FWV, FHV>;                                                                   \
+        if (dyn > 40 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);                     \
+        kern<<<g, kWsThreads, dyn, s>>>(at, tl, tr, tiles_x, out_align, fpc, bw, bh);                                                \
+    } while (0)
+                    if (a.W == 640 && a.H == 480 && !a.no_fixed_size) SA_WS_LAUNCH(640, 480);
+                    else if (a.W == 1920 && a.H == 1080 && !a.no_fixed_size) SA_WS_LAUNCH(1920, 1080);
+                    else SA_WS_LAUNCH(0, 0);
+#undef SA_WS_LAUNCH
                     return cudaGetLastError();
                 }
             }

@@ -82,7 +82,7 @@ def test_maps_absurd_calibrations(golden, calibs, tag):
 # ---- a3: rectified images -------------------------------------------------------------------------------------
 @pytest.mark.parametrize("name", ["calib_a", "calib_b", "calib_c_rational"])
 @pytest.mark.parametrize("variant", ["default", "tile_fastest", "force_direct", "force_generic", "persistent", "persistent_tile_fastest", "per_tile_cta", "no_bulk", "force_unaligned",
-                                     "no_l2_prefetch", "no_fixed_size"])
+                                     "no_l2_prefetch", "no_fixed_size", "no_align16", "no_align16_no_fixed_size"])
 def test_rectified_demo_bit_exact(golden, demo_pair, name, variant):
     g_ = golden["cases"]["demo_" + name]
     l, r = demo_pair
@@ -102,7 +102,9 @@ def test_rectified_demo_bit_exact(golden, demo_pair, name, variant):
             g.set_option("force_unaligned", 1)       # the W % 4 != 0 code path (funnel-shifted loads, run-wise word stores) on aligned frames
         if variant == "no_l2_prefetch":
             g.set_option("l2_prefetch", 0)
-        if variant == "no_fixed_size":
+        if variant.startswith("no_align16"):
+            g.set_option("no_align16", 1)             # the 4-byte-aligned frame loop where the 16-byte one would apply
+        if variant.endswith("no_fixed_size"):
             g.set_option("no_fixed_size", 1)          # the run-time-size instantiation of the batch kernel at 640x480
         if variant == "force_generic":
             g.set_option("force_generic", 1)
@@ -117,8 +119,9 @@ def test_rectified_scaled_bit_exact(golden, calibs, name):
     g_ = golden["cases"]["scaled_" + name]
     c, (W, H) = scaled_case(calibs, name)
     li, ri = O.synthetic_image(W, H, g_["image_seeds"][0]), O.synthetic_image(W, H, g_["image_seeds"][1])
-    for batch_loop, persistent, bulk in ((1, 0, 1), (1, 0, 0), (0, 4, 0), (0, 0, 0)):
+    for batch_loop, persistent, bulk, no16 in ((1, 0, 1, 0), (1, 0, 0, 0), (1, 0, 0, 1), (0, 4, 0, 0), (0, 0, 0, 0)):
         with geom(W, H, model="CREStereo") as g:
+            g.set_option("no_align16", no16)
             g.set_option("batch_loop", batch_loop)
             g.set_option("persistent", persistent)
             g.set_option("bulk", bulk)
@@ -126,6 +129,42 @@ def test_rectified_scaled_bit_exact(golden, calibs, name):
             g.rectify_preprocess(li[None], ri[None])
             assert md5(g.rectified(1, 0)[0]) == g_["rect_left"], name
             assert md5(g.rectified(1, 1)[0]) == g_["rect_right"], name
+
+
+@pytest.mark.parametrize("model,dtype", [("FastACVNet_plus", "f32"), ("RAFTStereo", "f16"), ("HitNet", "f16"), ("CREStereo", "f32")])
+@pytest.mark.parametrize("size", ["hd_1920x1080", "sd_1280x720"])
+def test_batches_on_the_16_byte_aligned_frame_loop(calibs, model, dtype, size):
+    """The 16-byte-aligned frame loop (rectify_batch16_kernel) on sizes with partial bottom tiles: 1920x1080 (its own
+    compile-time instantiation; 1080 = 67.5 tiles) and 1280x720 (run-time size), odd and even frame counts through the
+    two-frame unrolled loop, all four normalisations: rectified images and tensors exact against the oracle."""
+    from stereoalgorithms_b200.geometry import F16, F32, MODELS
+    if size == "hd_1920x1080":
+        c, (W, H) = scaled_case(calibs, size)
+    else:
+        W, H = 1280, 720
+        c = O.scale_calibration(calibs["calib_b"], 2.0, crop_y=(480 * 2.0 - H) / 2)
+    n = 5
+    L = np.stack([O.synthetic_image(W, H, 400 + i) for i in range(n)])
+    R = np.stack([O.synthetic_image(W, H, 500 + i) for i in range(n)])
+    (l1, l2), (r1, r2) = O.rectify_maps(c, (W, H))
+    npdt = np.float16 if dtype == "f16" else np.float32
+    with geom(W, H, model=model, dtype=F16 if dtype == "f16" else F32, max_batch=n) as g:
+        g.set_calibration(c)
+        g.set_option("batch_ctas", 1)                        # the whole batch in one CTA per tile: 5 frames = 2 unrolled pairs + 1
+        g.rectify_preprocess(L, R)
+        gl, gr = g.rectified(n, 0), g.rectified(n, 1)
+        t = g.tensor(n) if model == "HitNet" else (g.tensor(n, 0), g.tensor(n, 1))
+        for i in range(n):
+            wl, wr = OC.remap(L[i], l1, l2), OC.remap(R[i], r1, r2)
+            assert np.array_equal(gl[i], wl) and np.array_equal(gr[i], wr), i
+            want = O.preprocess(MODELS[model], wl, wr, npdt)
+            if model == "HitNet":
+                assert np.array_equal(t[i], want), i
+            else:
+                assert np.array_equal(t[0][i], want[0]) and np.array_equal(t[1][i], want[1]), i
+        g.set_option("batch_ctas", 1000)                     # one frame per CTA
+        g.rectify_preprocess(L[:2], R[:2])
+        assert np.array_equal(g.rectified(2, 1), gr[:2])
 
 
 def test_rectified_batch_device_input_and_pitch(calibs, demo_pair):
