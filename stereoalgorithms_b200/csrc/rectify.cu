@@ -839,7 +839,7 @@ __device__ __forceinline__ void ws_produce(const TileInfo ti, const CUtensorMap*
 // Consumer warps: blend frames [f0, f1) of one (tile, eye) out of the ring and store rectified bytes + tensors.
 template <int DTYPE, bool IDENT, bool WRITE_TENSOR, bool PART, int FW, int FH>
 __device__ __forceinline__ void ws_consume(const RectifyArgs& a, const TileInfo ti, int eye, int W, int H, int f0, int f1, int tx0, int ty0, uint32_t stage0,
-                                           uint32_t stage_b, uint64_t* s_full, uint64_t* s_empty, const typename TensorT<DTYPE>::type* s_lut)
+                                           uint32_t stage_b, uint64_t* s_full, uint64_t* s_empty, const uint32_t* s_lut)
 {
     using T = typename TensorT<DTYPE>::type;
     constexpr bool HBIAS = IDENT && WRITE_TENSOR && DTYPE == SA_F16;   // blend results carry the 0x6400 half-precision bias
@@ -864,7 +864,7 @@ __device__ __forceinline__ void ws_consume(const RectifyArgs& a, const TileInfo 
         for (int k = 0; k < 4; k++) {
             const uint32_t t = (!PART || ((pvalid >> k) & 1u)) ? __ldg(tmap + k * rstep) : 0u;
             const uint32_t fx = (t >> 12) & 31u, fy = (t >> 17) & 31u, off = t & 0xfffu;
-            const uint32_t ry = off / fw, rx = off - ry * fw;            // the table is laid out with the tile's own row length
+            const uint32_t ry = ((off >> 2) * ti.inv_gw) >> 20, rx = off - ry * fw;   // off / fw: the table is laid out with the tile's own row length
             toff[k] = stage0 + (ry * kWsStride + rx) * 4u;
             twt[k] = (32u - fx) | (fx << 8) | ((32u - fy) << 16) | (fy << 24);
         }
@@ -877,6 +877,7 @@ __device__ __forceinline__ void ws_consume(const RectifyArgs& a, const TileInfo 
     const size_t rect_frame_words = rect_frame / 4;
     constexpr uint32_t kAcc = HBIAS ? (512u + (0x6400u << 10)) : 512u;
     const int lane = tid & 31;
+    const char* const lut_r = reinterpret_cast<const char*>(s_lut) + 4 * (lane & 3);      // this lane's copy of the tables
 
     uint32_t st = 0, round = 0, so = 0;
     for (int f = f0; f < f1; f++) {
@@ -909,12 +910,21 @@ __device__ __forceinline__ void ws_consume(const RectifyArgs& a, const TileInfo 
             if (WRITE_TENSOR && pv) {
                 T r, g, b;
                 if (HBIAS) {
-                    const __half k1024 = __ushort_as_half((unsigned short)0x6400);
-                    r = (T)__hsub(__ushort_as_half((unsigned short)vR), k1024);
-                    g = (T)__hsub(__ushort_as_half((unsigned short)vG), k1024);
-                    b = (T)__hsub(__ushort_as_half((unsigned short)vB), k1024);
+                    // (half)(1024 + v) - 1024, one scalar subtraction per value (as a vector op the compiler pays for it in
+                    // byte-permutes that pack and unpack the pairs)
+                    unsigned short hr, hg, hb;
+                    asm("sub.rn.f16 %0, %1, %2;" : "=h"(hr) : "h"((unsigned short)vR), "h"((unsigned short)0x6400));
+                    asm("sub.rn.f16 %0, %1, %2;" : "=h"(hg) : "h"((unsigned short)vG), "h"((unsigned short)0x6400));
+                    asm("sub.rn.f16 %0, %1, %2;" : "=h"(hb) : "h"((unsigned short)vB), "h"((unsigned short)0x6400));
+                    r = (T)__ushort_as_half(hr); g = (T)__ushort_as_half(hg); b = (T)__ushort_as_half(hb);
+                } else if (IDENT) {
+                    normalise<DTYPE, IDENT, T>(nullptr, vB, vG, vR, r, g, b);
                 } else {
-                    normalise<DTYPE, IDENT, T>(s_lut, vB, vG, vR, r, g, b);
+                    // four interleaved copies of each table (entry e of copy j at word 4 e + j): the lanes of a warp are spread
+                    // over four disjoint sets of banks, which cuts the conflicts of 32 data-dependent look-ups from ~3.5 to ~2.3 wavefronts
+                    r = *reinterpret_cast<const T*>(lut_r + vR * 16u);
+                    g = *reinterpret_cast<const T*>(lut_r + 4096u + vG * 16u);
+                    b = *reinterpret_cast<const T*>(lut_r + 8192u + vB * 16u);
                 }
                 tp[k * rstep] = r; tp[k * rstep + plane] = g; tp[k * rstep + 2 * plane] = b;
             }
@@ -941,12 +951,17 @@ __global__ void __launch_bounds__(kWsThreads, SA_WS_MINB)
     // raw_b bytes (bw words x bh rows, rounded up to 128), then kWsStages BGRx stages of stage_b bytes (bh rows of kWsStride words)
     extern __shared__ __align__(128) uint8_t s_dyn[];
     __shared__ __align__(8) uint64_t s_rawfull[kWsRawStages], s_full[kWsStages], s_empty[kWsStages];
-    __shared__ T s_lut[IDENT ? 1 : 768];
+    __shared__ __align__(16) uint32_t s_lut[IDENT ? 4 : 3 * 256 * 4];   // [channel][entry][copy], one 32-bit word per value (ws_consume)
     const uint32_t raw_b = ((uint32_t)(bw * 4 * bh) + 127u) & ~127u, stage_b = (uint32_t)(kWsStrideB * bh);
     const int tid = threadIdx.x;
     if (!IDENT) {
         const T* lut = static_cast<const T*>(a.lut);
-        for (int i = tid; i < 768; i += kWsThreads) s_lut[i] = lut[i];
+        for (int i = tid; i < 768; i += kWsThreads) {
+            uint32_t bits = 0;
+            if (DTYPE == SA_F16) bits = __half_as_ushort(*reinterpret_cast<const __half*>(lut + i));
+            else bits = __float_as_uint(*reinterpret_cast<const float*>(lut + i));
+            *reinterpret_cast<uint4*>(&s_lut[4 * i]) = make_uint4(bits, bits, bits, bits);
+        }
     }
     const int W = FW ? FW : a.W, H = FH ? FH : a.H;
     const int eye = blockIdx.z & 1, chunk = blockIdx.z >> 1;
@@ -966,7 +981,7 @@ __global__ void __launch_bounds__(kWsThreads, SA_WS_MINB)
         for (int f = f0; f < f1; f++) {
             tile_sync<true>();
             tile_generic<DTYPE, IDENT, WRITE_TENSOR, true, true>(a, ti, eye, f, tx0, ty0, out_align, reinterpret_cast<uint32_t*>(s_dyn),
-                                                                 reinterpret_cast<uint32_t*>(s_dyn) + kFootprintWords, s_lut);   // (the launch reserves at least this much)
+                                                                 reinterpret_cast<uint32_t*>(s_dyn) + kFootprintWords, static_cast<const T*>(a.lut));   // (the launch reserves at least this much)
         }
         return;
     }
@@ -1253,7 +1268,8 @@ cudaError_t launch_rectify_t(const RectifyArgs& a, bool aligned4, int tiles_x, i
 #define SA_WS_LAUNCH(FWV, FHV)                                                                                                      \
     do {                                                                                                                            \
         auto kern = rectify_ws_kernel<DTYPE, IDENT, WT, FWV, FHV>;                                                                   \
-        if (dyn > 40 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);                     \
+        /* static (barriers, 12 KB of look-up tables) + dynamic beyond the 48 KB default needs the opt-in */                         \
+        if (dyn > 30 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);                     \
         kern<<<g, kWsThreads, dyn, s>>>(at, tl, tr, tiles_x, out_align, fpc, bw, bh);                                                \
     } while (0)
                     if (a.W == 640 && a.H == 480 && !a.no_fixed_size) SA_WS_LAUNCH(640, 480);
