@@ -1,4 +1,5 @@
 // C ABI of libstereo_geom.so (include/stereo_geom.h): handle, calibration, buffers, stage dispatch, copies.
+#include <algorithm>
 #include <cmath>
 #include <cstring>
 #include <new>
@@ -96,16 +97,17 @@ static int tiles_y(const sa_handle* h) { return (h->H + kTileH - 1) / kTileH; }
 // Largest staged footprint over both eyes: the box of the TMA rectify path.  Recomputed from the tile tables that exist.
 static int refresh_box(sa_handle* h)
 {
-    int mx[2] = {0, 0};
+    int mx[3] = {0, 0, 0};
     SA_CUDA(h, cudaMemcpy(mx, h->fp_max, sizeof mx, cudaMemcpyDeviceToHost));
     h->box_w = mx[0];
     h->box_h = mx[1];
+    h->unstaged_tiles = mx[2];
     return SA_OK;
 }
 
 static int compute_maps(sa_handle* h)
 {
-    SA_CUDA(h, cudaMemsetAsync(h->fp_max, 0, 2 * sizeof(int), h->stream));
+    SA_CUDA(h, cudaMemsetAsync(h->fp_max, 0, 3 * sizeof(int), h->stream));
     for (int eye = 0; eye < 2; eye++) {
         MapParams p{};
         double A[9];
@@ -119,7 +121,7 @@ static int compute_maps(sa_handle* h)
         {
             StageScope t(h, SA_STAGE_MAPS, h->stream);
             SA_CUDA(h, launch_init_maps(p, h->W, h->H, h->map1[eye], h->map2[eye], h->stream));
-            SA_CUDA(h, launch_tile_info(h->map1[eye], h->map2[eye], h->W, h->H, h->tiles[eye], h->tmap[eye], h->fp_max, tiles_x(h), tiles_y(h), (int)h->opt_force_direct, h->stream));
+            SA_CUDA(h, launch_tile_info(h->map1[eye], h->map2[eye], h->W, h->H, h->tiles[eye], h->tmap[eye], h->fp_max, tiles_x(h), tiles_y(h), (int)h->opt_force_direct, h->resize ? 1 : 0, h->stream));
             h->launches += 2;
         }
         h->have_maps[eye] = true;
@@ -178,6 +180,7 @@ static int stage_rectify(sa_handle* h, int f0, int n, const uint8_t* src_l, cons
 
     const uint8_t* net_src[2];
     size_t net_pitch, net_frame;
+    int fused = 0;                    // 1: the rectify launch also resized and wrote the tensors (+ the resized left image)
     if (rectify) {
         if (!h->have_maps[0] || !h->have_maps[1]) return fail(h, SA_ERR_NOT_READY, "no calibration / maps loaded (sa_load_calibration_yaml, sa_set_calibration or sa_set_maps)");
         RectifyArgs a{};
@@ -202,9 +205,18 @@ static int stage_rectify(sa_handle* h, int f0, int n, const uint8_t* src_l, cons
         a.no_fixed_size = (int)h->opt_no_fixed_size;
         a.no_align16 = (int)h->opt_no_align16;
         a.box_w = h->box_w; a.box_h = h->box_h;
+        a.unstaged_tiles = h->unstaged_tiles;
+        if (h->resize) {
+            a.rs_w = h->w; a.rs_h = h->h;
+            a.rs_area2x = (h->W == 2 * h->w && h->H == 2 * h->h) ? 1 : 0;
+            a.rs_tab_x = h->rs_x; a.rs_tab_y = h->rs_y; a.rs_nx = h->rs_nx; a.rs_ny = h->rs_ny;
+            a.rs_max_net = h->rs_max_net;
+            a.rs_net_left = h->net_u8[0] + (size_t)f0 * tplane * 3;
+            a.fused_resize = (int)h->opt_fused_resize;
+        }
         {
             StageScope t(h, SA_STAGE_RECTIFY, s);
-            SA_CUDA(h, launch_rectify(a, s, &h->launches));
+            SA_CUDA(h, launch_rectify(a, s, &h->launches, &fused));
         }
         net_src[0] = a.rect[0]; net_src[1] = a.rect[1];
         net_pitch = h->rect_pitch; net_frame = rect_frame;
@@ -217,8 +229,13 @@ static int stage_rectify(sa_handle* h, int f0, int n, const uint8_t* src_l, cons
         h->color_src[1] = rectify ? h->rect[1] : src_r;
         h->color_pitch = net_pitch; h->color_frame = net_frame;
     }
-    if (h->resize) {
+    if (h->resize && fused) {
         const size_t nf = tplane * 3;
+        if (f0 == 0) { h->color_src[0] = h->net_u8[0]; h->color_src[1] = nullptr; h->color_pitch = (size_t)h->w * 3; h->color_frame = nf; h->net_right_frames = 0; }
+    } else if (h->resize) {
+        const size_t nf = tplane * 3;
+        if (f0 == 0) h->net_right_frames = 0;
+        h->net_right_frames = std::max(h->net_right_frames, f0 + n);
         ResizeArgs r{};
         r.src[0] = net_src[0]; r.src[1] = net_src[1];
         r.dst[0] = h->net_u8[0] + (size_t)f0 * nf; r.dst[1] = h->net_u8[1] + (size_t)f0 * nf;
@@ -374,15 +391,18 @@ int sa_create(const sa_config* cfg, sa_handle** out)
     if (!(cfg->flags & SA_FLAG_NO_POINT_BUF)) A(dev_alloc(&h->points, N * npix * 6));
     if (!(cfg->flags & SA_FLAG_NO_HEATMAP_BUF)) A(dev_alloc(&h->heat, N * npix * 3));
     A(dev_alloc(&h->counts, N));
-    A(dev_alloc(&h->fp_max, 2));
-    if (ok) A(cudaMemset(h->fp_max, 0, 2 * sizeof(int)));
+    A(dev_alloc(&h->fp_max, 4));
+    if (ok) A(cudaMemset(h->fp_max, 0, 4 * sizeof(int)));
     A(dev_alloc(&h->minmax, N * 2));
     A(dev_alloc(&h->blk_counts, N * nblk));
     A(dev_alloc(&h->blk_offsets, N * nblk));
     A(dev_alloc(&h->blk_minmax, N * nblk * 2));
     A(dev_alloc(&h->lut32, 768));
     A(dev_alloc(&h->lut16, 768));
-    if (h->resize) { A(dev_alloc(&h->rs_x, 4 * (size_t)h->w)); A(dev_alloc(&h->rs_y, 4 * (size_t)h->h)); }
+    if (h->resize) {
+        A(dev_alloc(&h->rs_x, 4 * (size_t)h->w)); A(dev_alloc(&h->rs_y, 4 * (size_t)h->h));
+        A(dev_alloc(&h->rs_nx, (size_t)tiles_x(h) + 1)); A(dev_alloc(&h->rs_ny, (size_t)tiles_y(h) + 1));
+    }
     if (ok) {
         float lut[768];
         __half lut_h[768];
@@ -397,6 +417,24 @@ int sa_create(const sa_config* cfg, sa_handle** out)
             build_resize_table(h->h, h->H, &ty[0], &ty[h->h], &ty[2 * h->h], &ty[3 * h->h]);
             A(cudaMemcpy(h->rs_x, tx.data(), tx.size() * sizeof(int), cudaMemcpyHostToDevice));
             A(cudaMemcpy(h->rs_y, ty.data(), ty.size() * sizeof(int), cudaMemcpyHostToDevice));
+            // which network pixels a rectified tile owns (fused rectify + resize): those whose top-left tap (x0, y0) lies in it
+            auto owners = [](const int* s0, int D, int tiles, int tile, std::vector<int>& first) {
+                first.assign((size_t)tiles + 1, D);
+                int d = 0;
+                for (int t = 0; t <= tiles; t++) {
+                    while (d < D && s0[d] < t * tile) d++;                 // s0 is non-decreasing
+                    first[t] = d;
+                }
+                first[tiles] = D;
+                int most = 0;
+                for (int t = 0; t < tiles; t++) most = std::max(most, first[t + 1] - first[t]);
+                return most;
+            };
+            std::vector<int> nx, ny;
+            const int mx = owners(&tx[0], h->w, tiles_x(h), kTileW, nx), my = owners(&ty[0], h->h, tiles_y(h), kTileH, ny);
+            h->rs_max_net = mx * my;
+            A(cudaMemcpy(h->rs_nx, nx.data(), nx.size() * sizeof(int), cudaMemcpyHostToDevice));
+            A(cudaMemcpy(h->rs_ny, ny.data(), ny.size() * sizeof(int), cudaMemcpyHostToDevice));
         }
     }
     if (!ok) {
@@ -422,7 +460,7 @@ int sa_destroy(sa_handle* h)
         cudaFree(h->raw[e]); cudaFree(h->rect[e]); cudaFree(h->net_u8[e]); cudaFree(h->map1[e]); cudaFree(h->map2[e]); cudaFree(h->tiles[e]); cudaFree(h->tmap[e]);
     }
     cudaFree(h->tensor[0]); cudaFree(h->disp); cudaFree(h->points); cudaFree(h->heat); cudaFree(h->counts); cudaFree(h->minmax);
-    cudaFree(h->fp_max); cudaFree(h->blk_counts); cudaFree(h->blk_offsets); cudaFree(h->blk_minmax); cudaFree(h->lut32); cudaFree(h->lut16); cudaFree(h->rs_x); cudaFree(h->rs_y);
+    cudaFree(h->fp_max); cudaFree(h->blk_counts); cudaFree(h->blk_offsets); cudaFree(h->blk_minmax); cudaFree(h->lut32); cudaFree(h->lut16); cudaFree(h->rs_x); cudaFree(h->rs_y); cudaFree(h->rs_nx); cudaFree(h->rs_ny);
     for (int s = 0; s < SA_STAGE_COUNT_; s++) {
         for (auto ev : h->timer.begin[s]) cudaEventDestroy(ev);
         for (auto ev : h->timer.end[s]) cudaEventDestroy(ev);
@@ -603,7 +641,7 @@ int sa_set_maps(sa_handle* h, int eye, const int16_t* map1, const uint16_t* map2
     const size_t mpix = (size_t)h->W * h->H;
     SA_CUDA(h, cudaMemcpyAsync(h->map1[eye], map1, mpix * 4, cudaMemcpyHostToDevice, h->stream));
     SA_CUDA(h, cudaMemcpyAsync(h->map2[eye], map2, mpix * 2, cudaMemcpyHostToDevice, h->stream));
-    SA_CUDA(h, launch_tile_info(h->map1[eye], h->map2[eye], h->W, h->H, h->tiles[eye], h->tmap[eye], h->fp_max, tiles_x(h), tiles_y(h), (int)h->opt_force_direct, h->stream));
+    SA_CUDA(h, launch_tile_info(h->map1[eye], h->map2[eye], h->W, h->H, h->tiles[eye], h->tmap[eye], h->fp_max, tiles_x(h), tiles_y(h), (int)h->opt_force_direct, h->resize ? 1 : 0, h->stream));
     h->launches += 1;
     SA_CUDA(h, cudaStreamSynchronize(h->stream));
     h->have_maps[eye] = true;
@@ -767,7 +805,23 @@ int sa_copy_net_image(sa_handle* h, int n, int eye, uint8_t* out, int where, sa_
     SA_CHECK_N(h, n);
     if ((eye != 0 && eye != 1) || !out) return fail(h, SA_ERR_INVALID_ARG, "sa_copy_net_image: bad argument");
     if (!h->resize) return sa_copy_rectified(h, n, eye, out, where, stream);
-    return copy_out(h, out, h->net_u8[eye], (size_t)n * h->w * h->h * 3, where, pick(h, stream));
+    cudaStream_t s = pick(h, stream);
+    if (eye == 1 && h->net_right_frames < n) {
+        // the fused rectify + resize kernel writes only the LEFT resized image (stage B's colours); the right one is made on
+        // request from the rectified right image, with the stand-alone resize kernel
+        if (n > h->n_last) return fail(h, SA_ERR_NOT_READY, "sa_copy_net_image: only %d frame(s) processed", h->n_last);
+        ResizeArgs r{};
+        r.src[0] = r.src[1] = h->rect[1];
+        r.dst[0] = r.dst[1] = h->net_u8[1];
+        r.tab_x = h->rs_x; r.tab_y = h->rs_y;
+        r.src_pitch = h->rect_pitch; r.src_frame = h->rect_frame;
+        r.W = h->W; r.H = h->H; r.w = h->w; r.h = h->h; r.n = n;
+        r.area2x = (h->W == 2 * h->w && h->H == 2 * h->h) ? 1 : 0;
+        r.one_eye = 1;
+        SA_CUDA(h, launch_resize(r, s, &h->launches));
+        h->net_right_frames = n;
+    }
+    return copy_out(h, out, h->net_u8[eye], (size_t)n * h->w * h->h * 3, where, s);
 }
 
 int sa_copy_tensor(sa_handle* h, int n, int eye, void* out, int where, sa_stream stream)
@@ -1023,6 +1077,7 @@ int sa_set_option(sa_handle* h, const char* key, long value)
     else if (!std::strcmp(key, "l2_prefetch")) h->opt_l2_prefetch = value;
     else if (!std::strcmp(key, "frame_base")) h->opt_frame_base = value;
     else if (!std::strcmp(key, "no_align16")) h->opt_no_align16 = value;
+    else if (!std::strcmp(key, "fused_resize")) h->opt_fused_resize = value;
     else if (!std::strcmp(key, "chunk_taper")) h->opt_chunk_taper = value < 0 ? 0 : (value > 95 ? 95 : value);
     else return fail(h, SA_ERR_INVALID_ARG, "sa_set_option: unknown key '%s'", key);
     return SA_OK;

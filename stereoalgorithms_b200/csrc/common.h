@@ -79,6 +79,7 @@ struct sa_handle {
                                               // that every row starts 16-byte aligned and holds whole 4-pixel (12-byte) groups
     int* fp_max = nullptr;                    // device: {max footprint width, height} over staged full tiles of both eyes
     int box_w = 0, box_h = 0;                 // host copy of fp_max
+    int unstaged_tiles = 0;                   // tiles (both eyes) whose footprint does not fit the staging buffers
     float* lut32 = nullptr;                   // [3][256]
     __half* lut16 = nullptr;
     unsigned* minmax = nullptr;               // [N][2] ordered-uint encodings (min, ~max)
@@ -87,6 +88,10 @@ struct sa_handle {
     int* blk_offsets = nullptr;
     int* rs_x = nullptr;                      // resize tables: x0 x1 a0 a1 [w], y0 y1 b0 b1 [h]
     int* rs_y = nullptr;
+    int* rs_nx = nullptr;                     // fused resize: first network column / row owned by each tile column / row ([tiles + 1])
+    int* rs_ny = nullptr;
+    int rs_max_net = 0;
+    int net_right_frames = 0;                 // frames of net_u8[1] that are current (the fused kernel writes only the left image)
 
     // state
     const uint8_t* color_src[2] = {nullptr, nullptr};  // what reproject takes colours from / copy_rectified returns
@@ -112,6 +117,8 @@ struct sa_handle {
     long opt_l2_prefetch = -1;        // see RectifyArgs::l2_prefetch; -1 = automatic
     long opt_bulk = 0;                // rectify_tma_kernel when the frames are 16-byte aligned
     long opt_batch_loop = 1;          // rectify_batch_kernel (default); 0 = one CTA per (tile, eye, frame)
+    long opt_fused_resize = 0;        // 1 = one-launch rectify + resize + normalise (rectify_ws_kernel<..., RESIZE>) where it applies; 0 = three launches
+                                      // (measured on 64 pairs 1080p -> 640x480: 0.79 ms fused against 0.75 ms - the fused kernel is issue-bound)
     long opt_no_align16 = 0;          // 1 = keep the 4-byte-aligned frame loop even where the 16-byte one applies
     long opt_frame_base = 0;          // global index of this handle's frame 0 (sa_run_batch_multi: the stub numbers frames across shards)
     int sm_count = 148;
@@ -151,7 +158,7 @@ int parse_opencv_yaml(const char* path, std::vector<YamlMat>& out, std::string& 
 // kernels (each returns a cudaError_t from the launch)
 cudaError_t launch_init_maps(const MapParams& p, int W, int H, int* map1, uint16_t* map2, cudaStream_t s);
 cudaError_t launch_tile_info(const int* map1, const uint16_t* map2, int W, int H, TileInfo* tiles, uint32_t* tmap, int* fp_max, int tiles_x, int tiles_y,
-                             int force_direct, cudaStream_t s);
+                             int force_direct, int halo, cudaStream_t s);
 
 constexpr int kMaxChunks = 32;
 
@@ -181,11 +188,21 @@ struct RectifyArgs {
     size_t rect_pitch, rect_frame;     // bytes per row / per frame of the rectified output (rows padded, see sa_handle::rect_pitch)
     int force_unaligned;               // batch kernel: take the 2-byte-aligned code path even for 4-byte aligned frames (tests, tuning)
     int l2_prefetch;                   // batch kernel: prefetch.global.L2 of the frame this many iterations ahead (0 = off, < 0 = automatic)
-    int box_w, box_h;                  // largest staged footprint of the calibration over full tiles (pixels, rows), both eyes
+    int box_w, box_h;                  // largest staged footprint of the calibration (pixels, rows), both eyes
+    int unstaged_tiles;                // tiles whose footprint is not staged (bounds-checked path)
     int batch_ctas_per_sm;             // target number of CTAs per SM for the frame chunking of the batch kernel
     int no_align16;                    // batch kernel: do not take the 16-byte-aligned frame loop (tests, tuning)
+    // fused resize (rectify at W x H, tensors at rs_w x rs_h; launch_rectify reports through *fused whether it took this path)
+    int rs_w, rs_h, rs_area2x;         // network size (0 = no resize); 1 = exact 2x decimation (rounded 2x2 mean)
+    const int* rs_tab_x;               // x0 x1 a0 a1, each [rs_w]   (build_resize_table)
+    const int* rs_tab_y;               // y0 y1 b0 b1, each [rs_h]
+    const int* rs_nx;                  // [tiles_x + 1]: first network column whose left tap x0 lies in tile column i or beyond
+    const int* rs_ny;                  // [tiles_y + 1]: same for rows
+    int rs_max_net;                    // most network pixels any tile owns
+    uint8_t* rs_net_left;              // resized LEFT image [n][rs_h][rs_w][3] (stage B's colours); the right one is not written
+    int fused_resize;                  // 1: take the one-launch rectify + resize + normalise kernel where it applies (default: three launches, measured faster)
 };
-cudaError_t launch_rectify(const RectifyArgs& a, cudaStream_t s, long* launches);
+cudaError_t launch_rectify(const RectifyArgs& a, cudaStream_t s, long* launches, int* fused = nullptr);
 
 struct PreprocArgs {  // rectify = 0 path, and the second half of the resize path
     const uint8_t* src[2];
@@ -204,6 +221,7 @@ struct ResizeArgs {
     const int* tab_y;        // y0 y1 b0 b1, each [h]
     size_t src_pitch, src_frame;
     int W, H, w, h, n, area2x;
+    int one_eye;             // 1: src[0] / dst[0] only (n frames), not both eyes
 };
 cudaError_t launch_resize(const ResizeArgs& a, cudaStream_t s, long* launches);
 

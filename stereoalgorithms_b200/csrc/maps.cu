@@ -57,14 +57,17 @@ cudaError_t launch_init_maps(const MapParams& p, int W, int H, int* map1, uint16
 // One CTA per output tile: min/max of the (clamped) integer source coordinates of its pixels.
 __global__ void __launch_bounds__(256) tile_info_kernel(const int* __restrict__ map1, const uint16_t* __restrict__ map2, int W, int H,
                                                         TileInfo* __restrict__ tiles, uint32_t* __restrict__ tmap, int* __restrict__ fp_max, int tiles_x,
-                                                        int force_direct)
+                                                        int force_direct, int halo)
 {
     __shared__ TileInfo s_t;
     const int tile = blockIdx.x;
     const int tx0 = (tile % tiles_x) * kTileW, ty0 = (tile / tiles_x) * kTileH;
     int xmin = 1 << 20, xmax = -(1 << 20), ymin = 1 << 20, ymax = -(1 << 20);
-    for (int k = threadIdx.x; k < kTileW * kTileH; k += blockDim.x) {
-        int x = tx0 + (k % kTileW), y = ty0 + (k / kTileW);
+    // halo = 1 (handles that resize): the box also covers the taps of the pixel column right of the tile and the pixel row
+    // below it, which the fused rectify + resize kernel re-blends for the resize taps that straddle a tile edge
+    const int bw = kTileW + halo, bh = kTileH + halo;
+    for (int k = threadIdx.x; k < bw * bh; k += blockDim.x) {
+        int x = tx0 + (k % bw), y = ty0 + (k / bw);
         if (x < W && y < H) {
             int m = map1[(size_t)y * W + x];
             int sx = (int)(short)(m & 0xffff), sy = m >> 16;
@@ -100,12 +103,12 @@ __global__ void __launch_bounds__(256) tile_info_kernel(const int* __restrict__ 
         int h = ymax + 2 - ymin;
         t.x0 = (short)x0; t.y0 = (short)ymin; t.w = (short)w; t.h = (short)h;
         t.inv_gw = 0; t.flags = 0;
-        if (force_direct || w * h > kFootprintWords || w <= 0 || h <= 0) { t.w = 0; t.h = 0; }
+        if (force_direct || w * h > kFootprintWords || w <= 0 || h <= 0) { t.w = 0; t.h = 0; if (fp_max) atomicAdd(fp_max + 2, 1); }   // count of unstaged tiles
         else {
             const uint32_t gw = (uint32_t)w >> 2;
             t.inv_gw = ((1u << 20) + gw - 1) / gw;
             if (x0 >= 0 && ymin >= 0 && x0 + w <= W && ymin + h <= H) t.flags |= kTileInterior;
-            if (fp_max && tx0 + kTileW <= W && ty0 + kTileH <= H) { atomicMax(fp_max, w); atomicMax(fp_max + 1, h); }   // box of the TMA path
+            if (fp_max) { atomicMax(fp_max, w); atomicMax(fp_max + 1, h); }   // box of the tensor copies: the largest staged footprint, partial tiles included
         }
         tiles[tile] = t;
         s_t = t;
@@ -131,9 +134,9 @@ __global__ void __launch_bounds__(256) tile_info_kernel(const int* __restrict__ 
 }
 
 cudaError_t launch_tile_info(const int* map1, const uint16_t* map2, int W, int H, TileInfo* tiles, uint32_t* tmap, int* fp_max, int tiles_x, int tiles_y,
-                             int force_direct, cudaStream_t s)
+                             int force_direct, int halo, cudaStream_t s)
 {
-    tile_info_kernel<<<tiles_x * tiles_y, 256, 0, s>>>(map1, map2, W, H, tiles, tmap, fp_max, tiles_x, force_direct);
+    tile_info_kernel<<<tiles_x * tiles_y, 256, 0, s>>>(map1, map2, W, H, tiles, tmap, fp_max, tiles_x, force_direct, halo ? 1 : 0);
     return cudaGetLastError();
 }
 

@@ -176,7 +176,7 @@ __global__ void __launch_bounds__(256) disparity_u8_kernel(const float* __restri
 // ---- u8 resize (extension a8): OpenCV's fixed-point INTER_LINEAR for downscales ----------------------------
 __global__ void __launch_bounds__(256) resize_kernel(const ResizeArgs a)
 {
-    const int eye = blockIdx.y & 1, frame = blockIdx.y >> 1;
+    const int eye = a.one_eye ? 0 : (blockIdx.y & 1), frame = a.one_eye ? blockIdx.y : (blockIdx.y >> 1);
     const size_t npix = (size_t)a.w * a.h;
     const size_t p = (size_t)blockIdx.x * 256 + threadIdx.x;
     if (p >= npix) return;
@@ -259,7 +259,7 @@ cudaError_t launch_resize(const ResizeArgs& a, cudaStream_t s, long* launches)
 {
     if (a.n <= 0) return cudaSuccess;
     const size_t npix = (size_t)a.w * a.h;
-    resize_kernel<<<dim3((unsigned)((npix + 255) / 256), 2u * (unsigned)a.n), 256, 0, s>>>(a);
+    resize_kernel<<<dim3((unsigned)((npix + 255) / 256), (a.one_eye ? 1u : 2u) * (unsigned)a.n), 256, 0, s>>>(a);
     if (launches) ++*launches;
     return cudaGetLastError();
 }

@@ -739,8 +739,6 @@ __device__ __forceinline__ void rectify_batch_body(const RectifyArgs& a, int til
 constexpr int kWsStride = 100;                          // words per staged footprint row
 constexpr int kWsStrideB = kWsStride * 4;
 constexpr int kWsMaxW = 96, kWsMaxH = 32;               // largest footprint (pixels, rows)
-constexpr int kWsStageWords = kWsStride * kWsMaxH;      // 12.8 KB per stage
-constexpr int kWsStageB = kWsStageWords * 4;
 constexpr int kWsStages = 2;                            // BGRx stages: one being blended, one being filled
 constexpr int kWsRawStages = 3;                         // raw (packed BGR) stages: two tensor copies in flight while one is expanded
 constexpr int kWsProducers = 128;                       // four warps = one warpgroup (setmaxnreg works on whole warpgroups)
@@ -764,8 +762,8 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
         "{\n"
         ".reg .pred p;\n"
         "WAIT_%=:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra DONE_%=;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"      // (a suspend-time hint makes ptxas wrap the wait in a
+        "@p bra DONE_%=;\n"                                              // NANOSLEEP back-off loop: measured 2 % slower)
         "bra WAIT_%=;\n"
         "DONE_%=:\n"
         "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
@@ -783,6 +781,98 @@ __device__ __forceinline__ void put_unit(uint32_t addr, const uint4& u0, const u
     put4(addr + 16u, u0.w, u1.x, u1.y);
     put4(addr + 32u, u1.z, u1.w, u2.x);
     put4(addr + 48u, u2.y, u2.z, u2.w);
+}
+
+// ---- fused rectify -> resize -> normalise (extension a8) ---------------------------------------------------------------------------
+// Same rings and roles as above, plus: the consumer warps keep the tile they have just rectified in shared memory (one BGRx word
+// per pixel, 65 x 17: the tile plus the pixel column right of it and the pixel row below it, which are blended a second time
+// here because the bilinear taps of the resize straddle tile edges), and the PRODUCER warpgroup - idle most of the frame - resizes
+// out of it two frames later: OpenCV's 8-bit INTER_LINEAR (cv::resize, 11-bit coefficients; exact 2x decimation = rounded 2x2
+// mean), normalise, store the network planes.  The rectified image is written to global memory once and never read back; the
+// resized u8 image exists in registers only, except the LEFT one, which stage B needs for the point colours.  A tile owns the
+// network pixels whose top-left tap lies in it; their constants (tap offset, coefficients, output index) sit in a shared-memory
+// table built once per CTA.  No extra barrier is needed: when the consumers release BGRx stage (f mod 2) after blending frame f
+// they have also finished tile buffer (f mod 2), and they do not touch that buffer again before the producers - who resize frame
+// f - 2 right after they have handed over frame f, out of a ring of three tile buffers - say so.
+constexpr int kRtStride = 68;                                    // words per row of the shared rectified tile
+constexpr int kRtWords = kRtStride * (kTileH + 1);
+constexpr int kRtB = kRtWords * 4;
+constexpr int kRtBuffers = 3;                                    // tile of frame f in buffer f mod 3: written (f), waiting (f - 1), being resized (f - 2)
+
+struct WsResize {
+    uint32_t rt0;                 // shared-memory byte address of the two rectified-tile buffers
+    uint4* rz;                    // per owned network pixel: {tap byte offsets left | right << 16, a0 | a1 << 16, b0 | b1 << 16, y * w + x | dy << 31}
+    int nnet;                     // network pixels this tile owns
+};
+
+// Table of the network pixels tile (bx, by) owns; called by the 128 producer threads (p = 0..127).
+__device__ __forceinline__ int ws_resize_setup(const RectifyArgs& a, uint4* rz, int tx0, int ty0, int p)
+{
+    const int nx_lo = __ldg(a.rs_nx + blockIdx.x), nx_n = __ldg(a.rs_nx + blockIdx.x + 1) - nx_lo;
+    const int ny_lo = __ldg(a.rs_ny + blockIdx.y), ny_n = __ldg(a.rs_ny + blockIdx.y + 1) - ny_lo;
+    const int nnet = nx_n * ny_n;
+    const int w = a.rs_w, h = a.rs_h;
+    for (int q = p; q < nnet; q += kWsProducers) {
+        const int qy = q / nx_n, qx = q - qy * nx_n;
+        const int X = nx_lo + qx, Y = ny_lo + qy;
+        const int x0 = __ldg(a.rs_tab_x + X), x1 = __ldg(a.rs_tab_x + w + X), a0 = __ldg(a.rs_tab_x + 2 * w + X), a1 = __ldg(a.rs_tab_x + 3 * w + X);
+        const int y0 = __ldg(a.rs_tab_y + Y), y1 = __ldg(a.rs_tab_y + h + Y), b0 = __ldg(a.rs_tab_y + 2 * h + Y), b1 = __ldg(a.rs_tab_y + 3 * h + Y);
+        uint4 c;
+        const uint32_t o00 = (uint32_t)((y0 - ty0) * kRtStride + (x0 - tx0)) * 4u;          // byte offset of the top-left tap in a tile buffer
+        c.x = o00 | ((o00 + (uint32_t)(x1 - x0) * 4u) << 16);                                // ... and of the top-right one
+        c.y = (uint32_t)a0 | ((uint32_t)a1 << 16);
+        c.z = (uint32_t)b0 | ((uint32_t)b1 << 16);
+        c.w = (uint32_t)(Y * w + X) | ((uint32_t)(y1 - y0) << 31);                           // output index; bit 31: the bottom taps are one row down
+        rz[q] = c;
+    }
+    return nnet;
+}
+
+// Resize + normalise + store the owned network pixels of one frame out of tile buffer b; 128 producer threads.
+// tf / uf: this frame's tensor (plane 0) and resized left image (null for the right eye).
+template <int DTYPE, bool IDENT>
+__device__ __forceinline__ void ws_resize_frame(const WsResize& rs, typename TensorT<DTYPE>::type* __restrict__ tf, uint8_t* __restrict__ uf, size_t nplane, bool area,
+                                                uint32_t b, const typename TensorT<DTYPE>::type* s_lut, int p)
+{
+    using T = typename TensorT<DTYPE>::type;
+    const uint32_t rt = rs.rt0 + b * (uint32_t)kRtB;
+#ifdef SA_EXP_NO_RESIZE_BODY
+    if (nplane == 1)
+#endif
+#pragma unroll 1      // (unrolled by two, the three warps that own one pixel per lane execute the second, empty half as well)
+    for (int q = p; q < rs.nnet; q += kWsProducers) {
+        const uint4 c = rs.rz[q];
+        const uint32_t a00 = rt + (c.x & 0xffffu), a01 = rt + (c.x >> 16), dyb = (c.w >> 31) * (uint32_t)(kRtStride * 4), idx = c.w & 0x7fffffffu;
+        uint32_t p00, p01, p10, p11;
+        asm volatile("ld.shared.b32 %0, [%1];" : "=r"(p00) : "r"(a00));
+        asm volatile("ld.shared.b32 %0, [%1];" : "=r"(p01) : "r"(a01));
+        asm volatile("ld.shared.b32 %0, [%1];" : "=r"(p10) : "r"(a00 + dyb));
+        asm volatile("ld.shared.b32 %0, [%1];" : "=r"(p11) : "r"(a01 + dyb));
+        uint32_t v[3];
+        if (area) {                                                // rounded mean of the 2x2 block, per channel
+            const uint32_t tA = __byte_perm(p00, p01, 0x5140), tB = __byte_perm(p10, p11, 0x5140);       // B0 B1 G0 G1
+            const uint32_t tC = __byte_perm(p00, p01, 0x6262), tD = __byte_perm(p10, p11, 0x6262);       // R0 R1 R0 R1
+            v[0] = __dp4a(__byte_perm(tA, tB, 0x5410), 0x01010101u, 2u) >> 2;
+            v[1] = __dp4a(__byte_perm(tA, tB, 0x7632), 0x01010101u, 2u) >> 2;
+            v[2] = __dp4a(__byte_perm(tC, tD, 0x5410), 0x01010101u, 2u) >> 2;
+        } else {
+            const uint32_t b0s = c.z << 16, b1s = c.z & 0xffff0000u;
+#pragma unroll
+            for (int ch = 0; ch < 3; ch++) {
+                const uint32_t s = ch == 0 ? 0x7740u : (ch == 1 ? 0x7751u : 0x7762u);    // (p_left.ch, p_right.ch, 0, 0): byte 3 of a tile word is 0
+                const uint32_t T0 = __dp2a_lo(c.y, __byte_perm(p00, p01, s), 0u);           // p_left * a0 + p_right * a1
+                const uint32_t T1 = __dp2a_lo(c.y, __byte_perm(p10, p11, s), 0u);
+                // ((b0 * (T0 >> 4)) >> 16) + ((b1 * (T1 >> 4)) >> 16) + 2) >> 2 as OpenCV's VResizeLinear; at most 255: the coefficient
+                // pairs sum to at most 2049, so the two terms sum to at most 1021
+                v[ch] = (__umulhi(T0 >> 4, b0s) + __umulhi(T1 >> 4, b1s) + 2u) >> 2;
+            }
+        }
+        T r, g, bb;
+        normalise<DTYPE, IDENT, T>(s_lut, v[0], v[1], v[2], r, g, bb);
+        T* const t = tf + idx;
+        t[0] = r; t[nplane] = g; t[2 * nplane] = bb;
+        if (uf) { uint8_t* const u = uf + idx * 3u; u[0] = (uint8_t)v[0]; u[1] = (uint8_t)v[1]; u[2] = (uint8_t)v[2]; }
+    }
 }
 
 __device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* tm, int c0, int c1, int c2, uint64_t* bar)
@@ -804,8 +894,10 @@ __device__ __forceinline__ void tma_prefetch_3d(const CUtensorMap* tm, int c0, i
 // tensor prefetch.  No thread spends an instruction on global addresses, bounds or load latency.  The 64 producer lanes then
 // expand the box, 16 pixels (three 16-byte shared loads -> four 16-byte shared stores) per lane and round, into the BGRx stage
 // the consumers read.
-__device__ __forceinline__ void ws_produce(const TileInfo ti, const CUtensorMap* tm, int bw, int bh, int f0, int f1, int pfd, uint32_t raw0, uint32_t raw_stage_b,
-                                           uint32_t stage0, uint32_t stage_b, uint64_t* s_rawfull, uint64_t* s_full, uint64_t* s_empty)
+template <bool RESIZE, int DTYPE, bool IDENT>
+__device__ __forceinline__ void ws_produce(const RectifyArgs& a, const TileInfo ti, const CUtensorMap* tm, int eye, int bw, int bh, int f0, int f1, int pfd, uint32_t raw0,
+                                           uint32_t raw_stage_b, uint32_t stage0, uint32_t stage_b, uint64_t* s_rawfull, uint64_t* s_full, uint64_t* s_empty,
+                                           WsResize rs, const typename TensorT<DTYPE>::type* s_lut)
 {
     const int p = threadIdx.x - kRectThreads;                          // 0..127
     const int cx = 3 * (ti.x0 >> 2), cy = ti.y0;                       // box origin: word column (x0 is a multiple of 16 pixels = 12 words), row
@@ -838,12 +930,25 @@ __device__ __forceinline__ void ws_produce(const TileInfo ti, const CUtensorMap*
         asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4+32];" : "=r"(u2.x), "=r"(u2.y), "=r"(u2.z), "=r"(u2.w) : "r"(ra));
         put_unit(da, u0, u1, u2);
     };
-    uint32_t rs = 0, rround = 0;                                       // raw ring position
+    if (RESIZE) rs.nnet = ws_resize_setup(a, rs.rz, blockIdx.x * kTileW, blockIdx.y * kTileH, p);   // (each thread reads back only what it wrote)
+    using TT = typename TensorT<DTYPE>::type;
+    const size_t nplane = RESIZE ? (size_t)a.rs_w * a.rs_h : 0;
+    TT* tf = RESIZE ? static_cast<TT*>(a.tensor[eye]) + (size_t)f0 * a.tensor_frame : nullptr;      // tensor / resized left image of the next frame to resize
+    uint8_t* uf = (RESIZE && eye == 0) ? a.rs_net_left + (size_t)f0 * nplane * 3 : nullptr;
+    const bool area = RESIZE && a.rs_area2x != 0;
+    auto resize_next = [&](uint32_t b) {
+        ws_resize_frame<DTYPE, IDENT>(rs, tf, uf, nplane, area, b, s_lut, p);
+        tf += a.tensor_frame;
+        if (uf) uf += nplane * 3;
+    };
+    uint32_t rs_i = 0, rround = 0;                                     // raw ring position
+    uint32_t rzb = 0;                                                  // tile buffer of the next frame to resize
     for (int f = f0; f < f1; f++) {
         const uint32_t i = (uint32_t)(f - f0), st = i & 1u, round = i >> 1;
-        mbar_wait(&s_rawfull[rs], rround & 1u);                         // the packed bytes of frame f have landed
-        if (round) mbar_wait(&s_empty[st], (round - 1) & 1u);          // the consumers are done with the BGRx stage's previous frame
-        const uint32_t rsrc = raw0 + rs * raw_stage_b, rdst = stage0 + st * stage_b;
+        mbar_wait(&s_rawfull[rs_i], rround & 1u);                       // the packed bytes of frame f have landed
+        if (round) mbar_wait(&s_empty[st], (round - 1) & 1u);          // the consumers are done with the BGRx stage's previous frame (f - 2)
+                                                                        // ... and, fused resize, have left its rectified tile behind
+        const uint32_t rsrc = raw0 + rs_i * raw_stage_b, rdst = stage0 + st * stage_b;
         if (uraw[0] != 0xffffffffu) expand(rsrc + uraw[0], rdst + udst[0]);
         if (second && uraw[1] != 0xffffffffu) expand(rsrc + uraw[1], rdst + udst[1]);
         mbar_arrive(&s_full[st]);                                       // release: this lane's stores are visible to whoever acquires the barrier
@@ -852,12 +957,23 @@ __device__ __forceinline__ void ws_produce(const TileInfo ti, const CUtensorMap*
         if (p == 0) {
             if (f + kWsRawStages < f1) {
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy reads of the stage before the async-proxy write
-                mbar_expect_tx(&s_rawfull[rs], box_bytes);
-                tma_load_3d(reinterpret_cast<void*>(__cvta_shared_to_generic(rsrc)), tm, cx, cy, f + kWsRawStages, &s_rawfull[rs]);
+                mbar_expect_tx(&s_rawfull[rs_i], box_bytes);
+                tma_load_3d(reinterpret_cast<void*>(__cvta_shared_to_generic(rsrc)), tm, cx, cy, f + kWsRawStages, &s_rawfull[rs_i]);
             }
             if (pfd && f + kWsRawStages + pfd < f1) tma_prefetch_3d(tm, cx, cy, f + kWsRawStages + pfd);
         }
-        if (++rs == kWsRawStages) { rs = 0; ++rround; }
+        // fused resize: frame f is on its way to the consumers; now resize frame f - 2 out of its tile buffer (the consumers
+        // will not write that buffer again before frame f + 1 is handed over)
+        if (RESIZE && round) { resize_next(rzb); if (++rzb == kRtBuffers) rzb = 0; }
+        if (++rs_i == kWsRawStages) { rs_i = 0; ++rround; }
+    }
+    if (RESIZE) {                                                       // the last two frames: wait for the consumers, then resize
+        const int nf = f1 - f0;
+        for (int j = max(nf - 2, 0); j < nf; j++) {
+            mbar_wait(&s_empty[j & 1], (uint32_t)(j >> 1) & 1u);
+            resize_next(rzb);
+            if (++rzb == kRtBuffers) rzb = 0;
+        }
     }
 }
 
@@ -959,10 +1075,124 @@ __device__ __forceinline__ void ws_consume(const RectifyArgs& a, const TileInfo 
     }
 }
 
+// Consumer warps of the fused resize kernel: blend frames [f0, f1), store the rectified bytes, and leave every frame's tile
+// (+ halo column / row) as BGRx words in tile buffer (f - f0) mod 2 for the producers' resize (ws_resize_frame).
+template <bool PART, int FW, int FH>
+__device__ __forceinline__ void ws_consume_rt(const RectifyArgs& a, const TileInfo ti, int eye, int W, int H, int f0, int f1, int tx0, int ty0, uint32_t stage0,
+                                              uint32_t stage_b, uint64_t* s_full, uint64_t* s_empty, uint32_t rt0)
+{
+    const int tid = threadIdx.x;
+    const int lx = tid & (kTileW - 1), ly = tid >> 6;
+    const int pix0 = (ty0 + ly) * W + tx0 + lx;
+    const int rstep = 4 * W;
+    const size_t rect_pitch = FW ? (size_t)3 * FW : a.rect_pitch, rect_frame = FW ? (size_t)3 * FW * FH : a.rect_frame;
+    const int wstep = (int)rect_pitch;
+    uint32_t pvalid = 0xfu;
+    if (PART) {
+        pvalid = 0;
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+            if (tx0 + lx < W && ty0 + ly + 4 * k < H) pvalid |= 1u << k;
+    }
+    // own pixels (k = 0..3) and, for the first 81 threads, one halo pixel (k = 4): row 16 of the tile, then column 64, then the corner
+    uint32_t toff[5], twt[5];
+    {
+        const uint32_t* __restrict__ tmap = a.tmap[eye] + pix0;
+        const uint32_t fw = (uint32_t)ti.w;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const uint32_t t = (!PART || ((pvalid >> k) & 1u)) ? __ldg(tmap + k * rstep) : 0u;
+            const uint32_t fx = (t >> 12) & 31u, fy = (t >> 17) & 31u, off = t & 0xfffu;
+            const uint32_t ry = ((off >> 2) * ti.inv_gw) >> 20, rx = off - ry * fw;
+            toff[k] = stage0 + (ry * kWsStride + rx) * 4u;
+            twt[k] = (32u - fx) | (fx << 8) | ((32u - fy) << 16) | (fy << 24);
+        }
+    }
+    int hx = -1, hy = -1;                                            // halo pixel of this thread, tile coordinates
+    if (tid < kTileW) { hx = tid; hy = kTileH; }
+    else if (tid < kTileW + kTileH) { hx = kTileW; hy = tid - kTileW; }
+    else if (tid == kTileW + kTileH) { hx = kTileW; hy = kTileH; }
+    bool halo = hx >= 0 && tx0 + hx < W && ty0 + hy < H;
+    if (halo) {
+        // Needed at all?  Only the LAST network column / row a tile owns can have its left / top tap in the tile's last pixel
+        // column / row (x0, y0 are non-decreasing), and only if its right / bottom tap carries weight.
+        const int nx_hi = __ldg(a.rs_nx + blockIdx.x + 1), ny_hi = __ldg(a.rs_ny + blockIdx.y + 1);
+        bool need_col = false, need_row = false;
+        if (nx_hi > __ldg(a.rs_nx + blockIdx.x)) need_col = __ldg(a.rs_tab_x + nx_hi - 1) == tx0 + kTileW - 1 && __ldg(a.rs_tab_x + 3 * a.rs_w + nx_hi - 1) != 0;
+        if (ny_hi > __ldg(a.rs_ny + blockIdx.y)) need_row = __ldg(a.rs_tab_y + ny_hi - 1) == ty0 + kTileH - 1 && __ldg(a.rs_tab_y + 3 * a.rs_h + ny_hi - 1) != 0;
+        if (a.rs_area2x) need_col = need_row = false;                // 2 x 2 blocks start on even pixels: never across a tile edge
+        halo = (hx == kTileW ? need_col : true) && (hy == kTileH ? need_row : true);
+    }
+#ifdef SA_EXP_NO_HALO
+    halo = false;
+#endif
+    toff[4] = stage0;
+    twt[4] = 0;
+    if (halo) {
+        // the halo pixel belongs to a neighbouring tile: its taps, relative to THIS tile's box, from the maps themselves
+        const size_t mo = (size_t)(ty0 + hy) * W + tx0 + hx;
+        const int m1 = __ldg(a.map1[eye] + mo);
+        const uint32_t m2 = __ldg(a.map2[eye] + mo);
+        const int sx = max(-2, min(W, (int)(short)(m1 & 0xffff))), sy = max(-2, min(H, m1 >> 16));
+        const uint32_t fx = m2 & 31u, fy = (m2 >> 5) & 31u;
+        toff[4] = stage0 + (uint32_t)((sy - ti.y0) * kWsStride + (sx - ti.x0)) * 4u;
+        twt[4] = (32u - fx) | (fx << 8) | ((32u - fy) << 16) | (fy << 24);
+    }
+    const int m = tid & 3;
+    uint32_t sel = m == 0 ? 0x4210u : (m == 1 ? 0x5421u : 0x6542u);
+    asm volatile("" : "+r"(sel));
+    uint32_t* __restrict__ rp = rect_words(a.rect[eye] + (size_t)f0 * rect_frame, rect_pitch, ty0 + ly, tx0 + lx, m);
+    const size_t rect_frame_words = rect_frame / 4;
+    const uint32_t rt_mine = rt0 + (uint32_t)(ly * kRtStride + lx) * 4u;              // this thread's pixel k = 0 in tile buffer 0
+    const uint32_t rt_halo = rt0 + (uint32_t)(max(hy, 0) * kRtStride + max(hx, 0)) * 4u;
+    const int lane = tid & 31;
+
+    auto blend1 = [&](uint32_t ad, uint32_t wt) -> uint32_t {        // one rectified pixel as a BGRx word
+        uint32_t p00, p01, p10, p11;
+        asm volatile("ld.shared.b32 %0, [%1];" : "=r"(p00) : "r"(ad));
+        asm volatile("ld.shared.b32 %0, [%1+4];" : "=r"(p01) : "r"(ad));
+        asm volatile("ld.shared.b32 %0, [%1+%2];" : "=r"(p10) : "r"(ad), "n"(kWsStrideB));
+        asm volatile("ld.shared.b32 %0, [%1+%2];" : "=r"(p11) : "r"(ad), "n"(kWsStrideB + 4));
+        const uint32_t wx = wt & 0xffffu, wxh = wt << 16;
+        const uint32_t tBG = __byte_perm(p00, p01, 0x5140), tRR = __byte_perm(p00, p01, 0x6262);
+        const uint32_t bBG = __byte_perm(p10, p11, 0x5140), bRR = __byte_perm(p10, p11, 0x6262);
+        const uint32_t tB = __dp4a(tBG, wx, 0u), tG = __dp4a(tBG, wxh, 0u), tR = __dp4a(tRR, wx, 0u);
+        const uint32_t bB = __dp4a(bBG, wx, 0u), bG = __dp4a(bBG, wxh, 0u), bR = __dp4a(bRR, wx, 0u);
+        const uint32_t vB = __dp2a_hi(__byte_perm(tB, bB, 0x5410), wt, 512u) >> 10;
+        const uint32_t vG = __dp2a_hi(__byte_perm(tG, bG, 0x5410), wt, 512u) >> 10;
+        const uint32_t vR = __dp2a_hi(__byte_perm(tR, bR, 0x5410), wt, 512u) >> 10;
+        return vB | (vG << 8) | (vR << 16);
+    };
+
+    uint32_t st = 0, round = 0, so = 0, rb = 0;                        // rb: tile buffer of frame f = (f - f0) mod kRtBuffers
+    for (int f = f0; f < f1; f++) {
+        mbar_wait(&s_full[st], round & 1u);                             // frame f is staged - and tile buffer rb has been resized out of
+        const uint32_t rtb = rb * (uint32_t)kRtB;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const uint32_t v = blend1(toff[k] + so, twt[k]);
+            const bool pv = !PART || ((pvalid >> k) & 1u);
+            const uint32_t nb = __shfl_down_sync(0xffffffffu, v, 1);
+            if (m < 3 && pv) rp[k * wstep] = __byte_perm(v, nb, sel);
+            asm volatile("st.shared.b32 [%0], %1;" ::"r"(rt_mine + rtb + (uint32_t)(4 * k * kRtStride * 4)), "r"(v) : "memory");
+        }
+        if (halo) {
+            const uint32_t v = blend1(toff[4] + so, twt[4]);
+            asm volatile("st.shared.b32 [%0], %1;" ::"r"(rt_halo + rtb), "r"(v) : "memory");
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&s_empty[st]);                       // BGRx stage read, tile buffer written: both free for the producers
+        rp += rect_frame_words;
+        so += stage_b;
+        if (++st == kWsStages) { st = 0; so = 0; ++round; }
+        if (++rb == kRtBuffers) rb = 0;
+    }
+}
+
 #ifndef SA_WS_MINB
 #define SA_WS_MINB 4
 #endif
-template <int DTYPE, bool IDENT, bool WRITE_TENSOR, int FW = 0, int FH = 0>
+template <int DTYPE, bool IDENT, bool WRITE_TENSOR, int FW = 0, int FH = 0, bool RESIZE = false>
 __global__ void __launch_bounds__(kWsThreads, SA_WS_MINB)
     rectify_ws_kernel(const RectifyArgs a, const __grid_constant__ CUtensorMap tm_left, const __grid_constant__ CUtensorMap tm_right, int tiles_x, int out_align,
                       int frames_per_cta, int bw, int bh)
@@ -972,10 +1202,15 @@ __global__ void __launch_bounds__(kWsThreads, SA_WS_MINB)
     // raw_b bytes (bw words x bh rows, rounded up to 128), then kWsStages BGRx stages of stage_b bytes (bh rows of kWsStride words)
     extern __shared__ __align__(128) uint8_t s_dyn[];
     __shared__ __align__(8) uint64_t s_rawfull[kWsRawStages], s_full[kWsStages], s_empty[kWsStages];
-    __shared__ __align__(16) uint32_t s_lut[IDENT ? 4 : kLut4Words];   // [channel][entry][copy] (fill_lut4)
+    __shared__ __align__(16) uint32_t s_lut[(IDENT || RESIZE) ? 4 : kLut4Words];   // [channel][entry][copy] (fill_lut4)
+    __shared__ T s_lut_plain[(RESIZE && !IDENT) ? 768 : 1];            // fused resize: few look-ups per frame, plain [3][256] table
     const uint32_t raw_b = ((uint32_t)(bw * 4 * bh) + 127u) & ~127u, stage_b = (uint32_t)(kWsStrideB * bh);
     const int tid = threadIdx.x;
-    if (!IDENT) fill_lut4<DTYPE>(s_lut, a.lut, kWsThreads);
+    if (!IDENT && !RESIZE) fill_lut4<DTYPE>(s_lut, a.lut, kWsThreads);
+    if (!IDENT && RESIZE) {
+        const T* lut = static_cast<const T*>(a.lut);
+        for (int i = tid; i < 768; i += kWsThreads) s_lut_plain[i] = lut[i];
+    }
     const int W = FW ? FW : a.W, H = FH ? FH : a.H;
     const int eye = blockIdx.z & 1, chunk = blockIdx.z >> 1;
     const int f0 = a.chunk_tab ? a.chunk_begin[chunk] : chunk * frames_per_cta;
@@ -989,6 +1224,7 @@ __global__ void __launch_bounds__(kWsThreads, SA_WS_MINB)
     }
     __syncthreads();                                                    // barriers initialised, LUT in place; the only CTA-wide barrier
     const bool staged = ti.w > 0 && ti.w * 3 <= bw * 4 && ti.h <= bh;    // the footprint lies inside the box of the tensor copies
+    if (!staged && RESIZE) return;       // cannot happen: the host takes the fused path only when every tile's box fits (launch_rectify_t)
     if (!staged) {       // unstaged / oversized footprint: bounds-checked path, frame by frame, on the 256 consumer threads
         if (tid >= kRectThreads) return;
         for (int f = f0; f < f1; f++) {
@@ -999,17 +1235,27 @@ __global__ void __launch_bounds__(kWsThreads, SA_WS_MINB)
         return;
     }
     const uint32_t raw0 = smem_u32(s_dyn), stage0 = raw0 + kWsRawStages * raw_b;
+    WsResize rsz;
+    rsz.rt0 = stage0 + kWsStages * stage_b;
+    rsz.rz = reinterpret_cast<uint4*>(s_dyn + (rsz.rt0 - raw0) + kRtBuffers * kRtB);
+    rsz.nnet = 0;
     // Register split: the kernel is launched with 40 registers per thread (4 CTAs of 384 threads per SM); the producer
     // warpgroup gives back down to 24 - it holds one 48-byte unit and a few addresses - and the two consumer warpgroups take
-    // 48 each: 128 x 24 + 256 x 48 = 384 x 40.
+    // 48 each: 128 x 24 + 256 x 48 = 384 x 40.  (Fused resize: the producers also resize, everybody stays at 40.)
     if (tid >= kRectThreads) {
-        asm volatile("setmaxnreg.dec.sync.aligned.u32 24;");
-        ws_produce(ti, eye ? &tm_right : &tm_left, bw, bh, f0, f1, a.l2_prefetch >= 0 ? a.l2_prefetch : 2, raw0, raw_b, stage0, stage_b, s_rawfull, s_full, s_empty);
+        if (!RESIZE) asm volatile("setmaxnreg.dec.sync.aligned.u32 24;");
+        ws_produce<RESIZE, DTYPE, IDENT>(a, ti, eye ? &tm_right : &tm_left, eye, bw, bh, f0, f1, a.l2_prefetch >= 0 ? a.l2_prefetch : 2, raw0, raw_b, stage0, stage_b,
+                                         s_rawfull, s_full, s_empty, rsz, s_lut_plain);
+        return;
+    }
+    constexpr bool whole = FW && FW % kTileW == 0 && FH % kTileH == 0;   // no partial tiles at all
+    const bool full = whole || (tx0 + kTileW <= W && ty0 + kTileH <= H);
+    if (RESIZE) {
+        if (full) ws_consume_rt<false, FW, FH>(a, ti, eye, W, H, f0, f1, tx0, ty0, stage0, stage_b, s_full, s_empty, rsz.rt0);
+        else ws_consume_rt<true, FW, FH>(a, ti, eye, W, H, f0, f1, tx0, ty0, stage0, stage_b, s_full, s_empty, rsz.rt0);
         return;
     }
     asm volatile("setmaxnreg.inc.sync.aligned.u32 48;");
-    constexpr bool whole = FW && FW % kTileW == 0 && FH % kTileH == 0;   // no partial tiles at all
-    const bool full = whole || (tx0 + kTileW <= W && ty0 + kTileH <= H);
     if (full) ws_consume<DTYPE, IDENT, WRITE_TENSOR, false, FW, FH>(a, ti, eye, W, H, f0, f1, tx0, ty0, stage0, stage_b, s_full, s_empty, s_lut);
     else ws_consume<DTYPE, IDENT, WRITE_TENSOR, true, FW, FH>(a, ti, eye, W, H, f0, f1, tx0, ty0, stage0, stage_b, s_full, s_empty, s_lut);
 }
@@ -1224,8 +1470,9 @@ __global__ void __launch_bounds__(256) preprocess_lin_kernel(const PreprocArgs a
 
 inline bool lut_is_identity(int model) { return model == SA_MODEL_RAFTSTEREO || model == SA_MODEL_CRESTEREO; }
 
+// want_fused != nullptr: launch only the fused rectify + resize kernel, if it applies (*want_fused = 1), else nothing
 template <int DTYPE, bool IDENT, bool WT>
-cudaError_t launch_rectify_t(const RectifyArgs& a, bool aligned4, int tiles_x, int out_align, int fast_ok, dim3 grid, cudaStream_t s)
+cudaError_t launch_rectify_t(const RectifyArgs& a, bool aligned4, int tiles_x, int out_align, int fast_ok, dim3 grid, cudaStream_t s, int* want_fused = nullptr)
 {
     if (a.batch_loop && !a.force_generic && a.src_pitch * (size_t)a.H < (1u << 31) && (size_t)a.W * a.H * 3 < (1u << 30)) {
         const bool a4 = fast_ok && aligned4 && !a.force_unaligned;
@@ -1277,6 +1524,22 @@ cudaError_t launch_rectify_t(const RectifyArgs& a, bool aligned4, int tiles_x, i
                 if (encode_source_map(&tl, a.src[0], a.W, a.H, a.n, a.src_pitch, a.src_frame, bw, bh) &&
                     encode_source_map(&tr, a.src[1], a.W, a.H, a.n, a.src_pitch, a.src_frame, bw, bh)) {
                     size_t dyn = (size_t)kWsRawStages * (((size_t)bw * 4 * bh + 127) & ~(size_t)127) + (size_t)kWsStages * kWsStrideB * bh;
+                    if (want_fused) {
+                        // + two rectified-tile buffers and the table of the network pixels a tile owns
+                        dyn += (size_t)kRtBuffers * kRtB + 16 * (size_t)a.rs_max_net;
+                        if (dyn > 96 * 1024) return cudaSuccess;           // (a near-1:1 resize of a strongly distorted camera: three launches)
+#define SA_WS_RESIZE(FWV, FHV)                                                                                                      \
+    do {                                                                                                                            \
+        auto kern = rectify_ws_kernel<DTYPE, IDENT, true, FWV, FHV, true>;                                                           \
+        if (dyn > 30 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);                     \
+        kern<<<g, kWsThreads, dyn, s>>>(at, tl, tr, tiles_x, out_align, fpc, bw, bh);                                                \
+    } while (0)
+                        if (a.W == 1920 && a.H == 1080 && !a.no_fixed_size) SA_WS_RESIZE(1920, 1080);
+                        else SA_WS_RESIZE(0, 0);
+#undef SA_WS_RESIZE
+                        *want_fused = 1;
+                        return cudaGetLastError();
+                    }
                     const size_t generic_need = (size_t)(kFootprintWords + kTileH * kTileW * 3 / 4) * 4;   // scratch of the bounds-checked path
                     if (dyn < generic_need) dyn = generic_need;
 #define SA_WS_LAUNCH(FWV, FHV)                                                                                                      \
@@ -1293,12 +1556,14 @@ cudaError_t launch_rectify_t(const RectifyArgs& a, bool aligned4, int tiles_x, i
                     return cudaGetLastError();
                 }
             }
+            if (want_fused) return cudaSuccess;                        // the fused kernel does not apply: the caller takes the three-launch path
             if (a4 && a.W == 640 && a.H == 480 && !a.no_fixed_size) rectify_batch_kernel<DTYPE, IDENT, WT, true, 640, 480><<<g, kRectThreads, 0, s>>>(at, tiles_x, out_align, fpc);
             else if (a4) rectify_batch_kernel<DTYPE, IDENT, WT, true><<<g, kRectThreads, 0, s>>>(at, tiles_x, out_align, fpc);
             else rectify_batch_kernel<DTYPE, IDENT, WT, false><<<g, kRectThreads, 0, s>>>(at, tiles_x, out_align, fpc);
             return cudaGetLastError();
         }
     }
+    if (want_fused) return cudaSuccess;
     if (fast_ok && aligned4 && a.persistent_ctas > 0) {
         const int tiles_y = (a.H + kTileH - 1) / kTileH;
         const long long total = (long long)tiles_x * tiles_y * 2 * a.n;
@@ -1319,8 +1584,9 @@ static int ptr_align(const void* p) { return low_align((uintptr_t)p); }
 static int size_align(size_t v) { return low_align((uintptr_t)v); }
 static int min3(int a, int b, int c) { return a < b ? (a < c ? a : c) : (b < c ? b : c); }
 
-cudaError_t launch_rectify(const RectifyArgs& a, cudaStream_t s, long* launches)
+cudaError_t launch_rectify(const RectifyArgs& a, cudaStream_t s, long* launches, int* fused)
 {
+    if (fused) *fused = 0;
     if (a.n <= 0) return cudaSuccess;
     const int tiles_x = (a.W + kTileW - 1) / kTileW, tiles_y = (a.H + kTileH - 1) / kTileH;
     if (tiles_x > 65535 || tiles_y > 65535 || 2 * a.n > 65535) return cudaErrorInvalidConfiguration;
@@ -1335,6 +1601,16 @@ cudaError_t launch_rectify(const RectifyArgs& a, cudaStream_t s, long* launches)
                          !a.force_generic) ? 1 : 0;
     const bool ident = lut_is_identity(a.model);
     cudaError_t e;
+    if (fused && a.rs_w > 0 && a.fused_resize && a.unstaged_tiles == 0 && a.rs_net_left && a.tensor[0]) {
+        // rectify -> resize -> normalise in one launch (the rectified image never comes back from global memory)
+        int did = 0;
+#define SA_FUSED(DT, ID) e = launch_rectify_t<DT, ID, true>(a, aligned4, tiles_x, out_align, fast_ok, grid, s, &did)
+        if (a.dtype == SA_F16) { if (ident) SA_FUSED(SA_F16, true); else SA_FUSED(SA_F16, false); }
+        else { if (ident) SA_FUSED(SA_F32, true); else SA_FUSED(SA_F32, false); }
+#undef SA_FUSED
+        if (e != cudaSuccess) return e;
+        if (did) { *fused = 1; if (launches) ++*launches; return cudaSuccess; }
+    }
 #define SA_RECT(DT, ID, WT) e = launch_rectify_t<DT, ID, WT>(a, aligned4, tiles_x, out_align, fast_ok, grid, s)
     if (!a.write_tensor) SA_RECT(SA_F32, true, false);
     else if (a.dtype == SA_F16) { if (ident) SA_RECT(SA_F16, true, true); else SA_RECT(SA_F16, false, true); }
