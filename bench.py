@@ -392,6 +392,16 @@ def run_workload(args, wname, wl, rank, world, local, headline, sampler=None):
     calib = with_net_Q(wl, load_calib(wl))
     L, R = make_inputs(wl, n, rank)
     dL, dR = torch.from_numpy(L).cuda(), torch.from_numpy(R).cuda()
+    in_pitch = 0
+    if (3 * W) % 16 and not args.dense_rows:
+        # device frames as cudaMallocPitch / cv::cuda::GpuMat lay them out: every row starts 16-byte aligned (1242-wide: 3726 -> 3728
+        # bytes per row), which is what the tensor-copy kernel needs; --dense-rows times the packed layout (batch kernel) instead
+        in_pitch = (3 * W + 15) // 16 * 16
+        def pitched(t):
+            p = torch.zeros((n, H, in_pitch), dtype=torch.uint8, device="cuda")
+            p[:, :, :3 * W] = t.reshape(n, H, 3 * W)
+            return p
+        dL, dR = pitched(dL), pitched(dR)
     compact = args.reproject == "compact"
 
     g = StereoGeometry(W, H, model=wl["model"], dtype=F16 if wl["dtype"] == "f16" else F32, max_batch=n, gpu_id=local, flags=SL.FLAG_TIMING,
@@ -413,7 +423,7 @@ def run_workload(args, wname, wl, rank, world, local, headline, sampler=None):
     counts = torch.zeros(n, dtype=torch.int32, device="cuda") if compact else None
 
     def step():
-        g.rectify_preprocess(dL, dR, n=n, stream=sp)
+        g.rectify_preprocess(dL, dR, n=n, pitch=in_pitch, stream=sp)
         g.reproject(n, COMPACT if compact else DENSE, counts=counts, to_host=False, stream=sp)
         if args.heatmap:
             g.heatmap(n, to_host=False, stream=sp)
@@ -531,7 +541,8 @@ def run_workload(args, wname, wl, rank, world, local, headline, sampler=None):
                 pass
         res = {"value": value, "unit": UNIT, "ms_per_step": 1e3 * step_time / args.steps, "kernel_ms_per_step": 1e3 * dev_s / args.steps,
                "host_ms_per_step": 1e3 * elapsed / args.steps, "gpu_launches": launches, "roofline": roof, "e2e": e2e,
-               "config": workload_config(wname, wl, world, args.reproject, args.heatmap), "_wall": (t_wall0, t_wall1),
+               "config": dict(workload_config(wname, wl, world, args.reproject, args.heatmap), **({"device_row_pitch": in_pitch} if in_pitch else {})),
+               "_wall": (t_wall0, t_wall1),
                "dtype": "u8 fixed-point + f32 (%s tensors)" % wl["dtype"]}
         if compact:
             res["points_kept_per_frame"] = kept
@@ -562,6 +573,7 @@ def main():
     ap.add_argument("--no-ref-kernels", action="store_true", help="skip the reference-kernels-on-B200 row")
     ap.add_argument("--heatmap", action="store_true", help="include stage C in the step")
     ap.add_argument("--reproject", default="dense", choices=["dense", "compact"], help="stage B mode (compact = validity filter + compaction, extension a9)")
+    ap.add_argument("--dense-rows", action="store_true", help="device frames whose rows are not a multiple of 16 bytes (1242 wide) packed, not with a 16-byte-aligned row pitch")
     ap.add_argument("--frame-fastest", type=int, default=-1)
     ap.add_argument("--opt", action="append", default=[], help="library tuning option key=value (sa_set_option), repeatable")
     args = ap.parse_args()

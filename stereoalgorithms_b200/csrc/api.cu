@@ -203,7 +203,7 @@ static int stage_rectify(sa_handle* h, int f0, int n, const uint8_t* src_l, cons
         a.chunk_taper = (int)h->opt_chunk_taper;
         a.force_unaligned = (int)h->opt_force_unaligned;
         a.no_fixed_size = (int)h->opt_no_fixed_size;
-        a.no_align16 = (int)h->opt_no_align16;
+        a.no_align16 = (h->opt_no_align16 || !h->opt_bulk) ? 1 : 0;
         a.box_w = h->box_w; a.box_h = h->box_h;
         a.unstaged_tiles = h->unstaged_tiles;
         if (h->resize) {
@@ -371,8 +371,10 @@ int sa_create(const sa_config* cfg, sa_handle** out)
     // B, resize, sa_copy_rectified).
     h->rect_pitch = h->W % 4 == 0 ? (size_t)h->W * 3 : ((size_t)((h->W + 3) / 4) * 12 + 15) / 16 * 16;
     h->rect_frame = h->rect_pitch * h->H;
+    // uploaded frames: rows padded to 16 bytes, so that host input of any even width (1242 ...) takes the tensor-copy kernel
+    h->raw_pitch = ((size_t)h->W * 3 + 15) / 16 * 16;
     for (int eye = 0; eye < 2 && ok; eye++) {
-        A(dev_alloc(&h->raw[eye], N * img));
+        A(dev_alloc(&h->raw[eye], N * h->raw_pitch * h->H));
         A(dev_alloc(&h->rect[eye], N * h->rect_frame));
         if (h->resize) A(dev_alloc(&h->net_u8[eye], N * npix * 3));
         A(dev_alloc(&h->map1[eye], mpix));
@@ -673,13 +675,16 @@ int sa_rectify_preprocess(sa_handle* h, int n, const uint8_t* left, const uint8_
     cudaStream_t s = pick(h, stream);
     const uint8_t* src[2] = {left, right};
     size_t src_pitch = pitch;
+    // rows padded to 16 bytes for the rectifying kernels (tensor copies need aligned rows); dense for the plain preprocess,
+    // whose linear four-pixel kernel wants contiguous frames
+    const size_t up_pitch = rectify ? h->raw_pitch : row;
     if (where == SA_HOST) {
         for (int e = 0; e < 2; e++) {
-            if (pitch == row) SA_CUDA(h, cudaMemcpyAsync(h->raw[e], src[e], (size_t)n * h->H * row, cudaMemcpyHostToDevice, s));
-            else SA_CUDA(h, cudaMemcpy2DAsync(h->raw[e], row, src[e], pitch, row, (size_t)n * h->H, cudaMemcpyHostToDevice, s));
+            if (pitch == row && up_pitch == row) SA_CUDA(h, cudaMemcpyAsync(h->raw[e], src[e], (size_t)n * h->H * row, cudaMemcpyHostToDevice, s));
+            else SA_CUDA(h, cudaMemcpy2DAsync(h->raw[e], up_pitch, src[e], pitch, row, (size_t)n * h->H, cudaMemcpyHostToDevice, s));
             src[e] = h->raw[e];
         }
-        src_pitch = row;
+        src_pitch = up_pitch;
     }
     h->n_last = n;
     h->minmax_valid = 0;
@@ -916,6 +921,8 @@ static int run_batch_chunks(sa_handle* h, int n, const uint8_t* left, const uint
                             float* disparity, uint8_t* rect_left, uint8_t* rect_right, uint8_t* heatmap)
 {
     const size_t img = (size_t)h->W * h->H * 3, npix = (size_t)h->w * h->h, dfl = disp_frame_floats(h);
+    const size_t up_pitch = rectify ? h->raw_pitch : (size_t)h->W * 3; // rows padded to 16 bytes for the rectifying kernels, dense otherwise
+    const size_t rawf = up_pitch * h->H;                              // one uploaded frame
     const int chunk = (int)(h->opt_chunk > 0 ? h->opt_chunk : 8);
     const int nchunks = (n + chunk - 1) / chunk;
     uint8_t* rect_out[2] = {rect_left, rect_right};
@@ -925,12 +932,14 @@ static int run_batch_chunks(sa_handle* h, int n, const uint8_t* left, const uint
         cudaEvent_t up = pool_event(h, 2 * (size_t)c), done = pool_event(h, 2 * (size_t)c + 1);
         if (!up || !done) return fail(h, SA_ERR_CUDA, "sa_run_batch: cannot create events");
         // upload (cudaMemcpyAsync H2D x2, TRTFastACVNet_plus.cpp:130-131)
-        for (int e = 0; e < 2; e++)
-            SA_CUDA(h, cudaMemcpyAsync(h->raw[e] + (size_t)f0 * img, host_in[e] + (size_t)f0 * img, (size_t)m * img, cudaMemcpyHostToDevice, h->s_h2d));
+        for (int e = 0; e < 2; e++) {
+            if (up_pitch == (size_t)h->W * 3) SA_CUDA(h, cudaMemcpyAsync(h->raw[e] + (size_t)f0 * img, host_in[e] + (size_t)f0 * img, (size_t)m * img, cudaMemcpyHostToDevice, h->s_h2d));
+            else SA_CUDA(h, cudaMemcpy2DAsync(h->raw[e] + (size_t)f0 * rawf, up_pitch, host_in[e] + (size_t)f0 * img, (size_t)h->W * 3, (size_t)h->W * 3, (size_t)m * h->H, cudaMemcpyHostToDevice, h->s_h2d));
+        }
         SA_CUDA(h, cudaEventRecord(up, h->s_h2d));
         SA_CUDA(h, cudaStreamWaitEvent(h->stream, up, 0));
         // stage A
-        int rc = stage_rectify(h, f0, m, h->raw[0] + (size_t)f0 * img, h->raw[1] + (size_t)f0 * img, (size_t)h->W * 3, img, rectify, h->stream);
+        int rc = stage_rectify(h, f0, m, h->raw[0] + (size_t)f0 * rawf, h->raw[1] + (size_t)f0 * rawf, up_pitch, rawf, rectify, h->stream);
         if (rc != SA_OK) return rc;
         // network slot (enqueueV3, TRTFastACVNet_plus.cpp:152)
         const size_t tframe = (h->cfg.model == SA_MODEL_HITNET ? 6 : 3) * npix * h->tensor_elt;

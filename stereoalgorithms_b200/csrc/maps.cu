@@ -94,10 +94,10 @@ __global__ void __launch_bounds__(256) tile_info_kernel(const int* __restrict__ 
         }
         TileInfo t;
         // Footprint columns start and end on a multiple of 4 pixels (12 bytes = 3 words: the staging unit of the 4-byte-aligned
-        // paths) - or of 16 pixels (48 bytes = three 16-byte loads, the unit of the 16-byte-aligned batch path) when the image
-        // width allows every row to start 16-byte aligned.  Wider by 12 pixels on average; rows are fetched in 32-byte
+        // paths) - or of 16 pixels (48 bytes = three 16-byte loads, the unit of the warp-specialised kernel) when the image
+        // width allows the tensor-copy path at all.  Wider by 12 pixels on average; rows are fetched in 32-byte
         // sectors anyway.
-        const int al = (W % 16 == 0) ? 15 : 3;
+        const int al = (W % 2 == 0) ? 15 : 3;    // (even widths can take the tensor-copy path if their rows are padded to 16 bytes)
         int x0 = xmin & ~al;                     // floor (also for negatives)
         int w = ((xmax + 2 - x0) + al) & ~al;    // taps reach sx+1
         int h = ymax + 2 - ymin;

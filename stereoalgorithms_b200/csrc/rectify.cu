@@ -900,7 +900,7 @@ __device__ __forceinline__ void ws_produce(const RectifyArgs& a, const TileInfo 
                                            WsResize rs, const typename TensorT<DTYPE>::type* s_lut)
 {
     const int p = threadIdx.x - kRectThreads;                          // 0..127
-    const int cx = 3 * (ti.x0 >> 2), cy = ti.y0;                       // box origin: word column (x0 is a multiple of 16 pixels = 12 words), row
+    const int cx = 6 * (ti.x0 >> 2), cy = ti.y0;                       // box origin: column in 16-bit elements (x0 is a multiple of 16 pixels = 48 bytes), row
     const uint32_t rowb = (uint32_t)bw * 4u, box_bytes = rowb * (uint32_t)bh;
     const int nunits = (bw / 12) * bh;                                 // 16-pixel units in the box
     if (p == 0) {
@@ -1297,11 +1297,13 @@ static bool encode_source_map(CUtensorMap* tm, const uint8_t* base, int W, int H
         if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess) fn = (encode_fn)p;
     }
     if (!fn) return false;
-    const cuuint64_t dims[3] = {(cuuint64_t)(3 * W / 4), (cuuint64_t)H, (cuuint64_t)n};
+    // 16-bit elements: a row is 3W/2 of them for every even W (1242 included; 4-byte elements would need W % 4 == 0), a box row of
+    // up to 96 pixels is 144 <= 256 of them, and bytes beyond 3W - the row padding, the next row - are outside the tensor: zero-filled
+    const cuuint64_t dims[3] = {(cuuint64_t)(3 * W / 2), (cuuint64_t)H, (cuuint64_t)n};
     const cuuint64_t strides[2] = {(cuuint64_t)pitch, (cuuint64_t)frame};
-    const cuuint32_t box[3] = {(cuuint32_t)bw, (cuuint32_t)bh, 1u};
+    const cuuint32_t box[3] = {(cuuint32_t)(2 * bw), (cuuint32_t)bh, 1u};
     const cuuint32_t estr[3] = {1u, 1u, 1u};
-    return fn(tm, CU_TENSOR_MAP_DATA_TYPE_UINT32, 3, const_cast<uint8_t*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+    return fn(tm, CU_TENSOR_MAP_DATA_TYPE_UINT16, 3, const_cast<uint8_t*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
               CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
@@ -1476,6 +1478,8 @@ cudaError_t launch_rectify_t(const RectifyArgs& a, bool aligned4, int tiles_x, i
 {
     if (a.batch_loop && !a.force_generic && a.src_pitch * (size_t)a.H < (1u << 31) && (size_t)a.W * a.H * 3 < (1u << 30)) {
         const bool a4 = fast_ok && aligned4 && !a.force_unaligned;
+        // the warp-specialised kernel does not need W % 4 == 0 (fast_ok does: the batch kernel's 12-byte groups)
+        const bool fast_ok_any_w = out_align >= 4 && !a.force_generic;
         const int tiles_y = (a.H + kTileH - 1) / kTileH;
         // frames per CTA.  Many short CTAs balance better (partial tiles at the image edge take longer than full ones, and
         // the last wave of a launch is only as fast as its slowest CTA); long CTAs amortise the per-tile set-up.  Measured
@@ -1515,8 +1519,10 @@ cudaError_t launch_rectify_t(const RectifyArgs& a, bool aligned4, int tiles_x, i
         if (2 * chunks <= 65535) {
             const dim3 g((unsigned)tiles_x, (unsigned)tiles_y, 2u * (unsigned)chunks);
             // 16-byte-aligned input and footprints that fit a ring stage: the warp-specialised kernel
-            const bool a16 = a4 && !a.no_align16 && a.W % 16 == 0 && a.src_pitch % 16 == 0 && a.src_frame % 16 == 0 && ((uintptr_t)a.src[0] | (uintptr_t)a.src[1]) % 16 == 0 &&
-                             a.box_w > 0 && a.box_w <= kWsMaxW && a.box_h <= kWsMaxH;
+            // (any even width: what matters is that every ROW starts 16-byte aligned - dense 640 / 1920 / 3840-wide frames, or a
+            // padded pitch such as cudaMallocPitch / cv::cuda::GpuMat give a 1242-wide one)
+            const bool a16 = fast_ok_any_w && !a.no_align16 && !a.force_unaligned && a.W % 2 == 0 && a.src_pitch % 16 == 0 && a.src_frame % 16 == 0 &&
+                             ((uintptr_t)a.src[0] | (uintptr_t)a.src[1]) % 16 == 0 && a.box_w > 0 && a.box_w % 16 == 0 && a.box_w <= kWsMaxW && a.box_h <= kWsMaxH;
             if (a16) {
                 // box of the tensor copies = the largest footprint of the calibration (a multiple of 16 pixels wide), in 4-byte words
                 const int bw = a.box_w * 3 / 4, bh = a.box_h;

@@ -133,10 +133,10 @@ def test_rectified_scaled_bit_exact(golden, calibs, name):
 
 @pytest.mark.parametrize("model,dtype", [("FastACVNet_plus", "f32"), ("RAFTStereo", "f16"), ("HitNet", "f16"), ("CREStereo", "f32")])
 @pytest.mark.parametrize("size", ["hd_1920x1080", "sd_1280x720"])
-def test_batches_on_the_16_byte_aligned_frame_loop(calibs, model, dtype, size):
-    """The 16-byte-aligned frame loop (rectify_batch16_kernel) on sizes with partial bottom tiles: 1920x1080 (its own
-    compile-time instantiation; 1080 = 67.5 tiles) and 1280x720 (run-time size), odd and even frame counts through the
-    two-frame unrolled loop, all four normalisations: rectified images and tensors exact against the oracle."""
+def test_batches_on_the_warp_specialised_kernel(calibs, model, dtype, size):
+    """rectify_ws_kernel (tensor copies, producer / consumer warps, two- and three-stage rings) on sizes with partial bottom
+    tiles: 1920x1080 (its own compile-time instantiation; 1080 = 67.5 tiles) and 1280x720 (run-time size), frame counts that
+    wrap the rings unevenly, all four normalisations: rectified images and tensors exact against the oracle."""
     from stereoalgorithms_b200.geometry import F16, F32, MODELS
     if size == "hd_1920x1080":
         c, (W, H) = scaled_case(calibs, size)
@@ -698,10 +698,14 @@ def test_side_by_side_capture_frame(calibs, demo_pair):
 
 @pytest.mark.parametrize("size", [(1242, 375), (638, 50), (333, 77), (67, 19), (131, 33), (1241, 40)])
 @pytest.mark.parametrize("l2_prefetch", [2, 0])
-def test_rectified_unaligned_widths_batches(calibs, size, l2_prefetch):
+@pytest.mark.parametrize("source", ["host", "host_batch_kernel", "device_dense", "device_pitched"])
+def test_rectified_unaligned_widths_batches(calibs, size, l2_prefetch, source):
     """Widths that are not a multiple of 4: rows (and, for odd W*H, frames) start at every byte alignment, so the batch
     kernel's funnel-shifted loads and its run-wise aligned-word stores (head/tail bytes at warp and row ends, partial tiles
-    at the right edge) see all four cases; several frames per CTA; tensors of the last frame checked too."""
+    at the right edge) see all four cases; several frames per CTA; tensors of the last frame checked too.
+    source: host frames are uploaded with rows padded to 16 bytes, so even widths take the tensor-copy kernel ("host"; with
+    bulk = 0 the batch kernel: "host_batch_kernel"); packed device frames take the batch kernel ("device_dense"); device frames
+    with a 16-byte-aligned row pitch (cudaMallocPitch style) the tensor-copy kernel again ("device_pitched")."""
     W, H = size
     s = W / 640
     c = O.scale_calibration(calibs["calib_a"], s, crop_y=(480 * s - H) / 2)
@@ -713,8 +717,21 @@ def test_rectified_unaligned_widths_batches(calibs, size, l2_prefetch):
     with geom(W, H, model="HitNet", max_batch=n) as g:
         g.set_option("l2_prefetch", l2_prefetch)
         g.set_option("batch_ctas", 1)                     # all frames in one CTA
+        g.set_option("bulk", 0 if source == "host_batch_kernel" else 1)
         g.set_calibration(c)
-        g.rectify_preprocess(L, R)
+        if source.startswith("host"):
+            g.rectify_preprocess(L, R)
+        elif source == "device_dense":
+            import torch
+            g.rectify_preprocess(torch.from_numpy(L).cuda(), torch.from_numpy(R).cuda())
+        else:
+            import torch
+            pitch = (3 * W + 15) // 16 * 16 + 16
+            dl = torch.full((n, H, pitch), 0x5A, dtype=torch.uint8, device="cuda")      # padding bytes that must never be sampled
+            dr = torch.full((n, H, pitch), 0xA5, dtype=torch.uint8, device="cuda")
+            dl[:, :, :3 * W] = torch.from_numpy(L.reshape(n, H, 3 * W)).cuda()
+            dr[:, :, :3 * W] = torch.from_numpy(R.reshape(n, H, 3 * W)).cuda()
+            g.rectify_preprocess(dl, dr, n=n, pitch=pitch)
         gl, gr = g.rectified(n, 0), g.rectified(n, 1)
         for i in range(n):
             assert np.array_equal(gl[i], OC.remap(L[i], l1, l2)), (size, i)
