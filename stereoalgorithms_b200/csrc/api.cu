@@ -142,6 +142,15 @@ static cudaError_t dev_alloc(T** p, size_t count) { return cudaMalloc((void**)p,
 
 static cudaStream_t pick(sa_handle* h, sa_stream s) { return s ? (cudaStream_t)s : h->stream; }
 
+// Row pitch of host frames on the device.  Dense - one linear copy per chunk - unless padding the rows to 16 bytes is what lets
+// the tensor-copy rectify kernel run: widths that are not a multiple of 16 with option bulk = 2 (a 2-D copy of 3726-byte rows
+// costs the 1242x375 end-to-end path 20 % of its PCIe rate, so it is not done for nothing).
+static size_t upload_pitch(const sa_handle* h, int rectify)
+{
+    const size_t row = (size_t)h->W * 3;
+    return (rectify && h->opt_bulk >= 2 && h->W % 2 == 0) ? h->raw_pitch : row;
+}
+
 // where == host: async copy + (for device->host results) a synchronise so the caller may read at once.
 static int copy_out(sa_handle* h, void* dst, const void* src, size_t bytes, int where, cudaStream_t s)
 {
@@ -675,9 +684,7 @@ int sa_rectify_preprocess(sa_handle* h, int n, const uint8_t* left, const uint8_
     cudaStream_t s = pick(h, stream);
     const uint8_t* src[2] = {left, right};
     size_t src_pitch = pitch;
-    // rows padded to 16 bytes for the rectifying kernels (tensor copies need aligned rows); dense for the plain preprocess,
-    // whose linear four-pixel kernel wants contiguous frames
-    const size_t up_pitch = rectify ? h->raw_pitch : row;
+    const size_t up_pitch = upload_pitch(h, rectify);
     if (where == SA_HOST) {
         for (int e = 0; e < 2; e++) {
             if (pitch == row && up_pitch == row) SA_CUDA(h, cudaMemcpyAsync(h->raw[e], src[e], (size_t)n * h->H * row, cudaMemcpyHostToDevice, s));
@@ -921,7 +928,7 @@ static int run_batch_chunks(sa_handle* h, int n, const uint8_t* left, const uint
                             float* disparity, uint8_t* rect_left, uint8_t* rect_right, uint8_t* heatmap)
 {
     const size_t img = (size_t)h->W * h->H * 3, npix = (size_t)h->w * h->h, dfl = disp_frame_floats(h);
-    const size_t up_pitch = rectify ? h->raw_pitch : (size_t)h->W * 3; // rows padded to 16 bytes for the rectifying kernels, dense otherwise
+    const size_t up_pitch = upload_pitch(h, rectify);
     const size_t rawf = up_pitch * h->H;                              // one uploaded frame
     const int chunk = (int)(h->opt_chunk > 0 ? h->opt_chunk : 8);
     const int nchunks = (n + chunk - 1) / chunk;

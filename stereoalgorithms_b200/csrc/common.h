@@ -116,7 +116,8 @@ struct sa_handle {
     long opt_no_fixed_size = 0;
     long opt_chunk_taper = 50;        // see RectifyArgs::chunk_taper (measured: 1-2 % on the 640x480 and 1242x375 workloads, neutral at 1080p)
     long opt_l2_prefetch = -1;        // see RectifyArgs::l2_prefetch; -1 = automatic
-    long opt_bulk = 1;                // 1 = rectify_ws_kernel (tensor copies + warp specialisation) when the frames are 16-byte aligned; 0 = same as no_align16
+    long opt_bulk = 1;                // 1 = rectify_ws_kernel (tensor copies + warp specialisation) when the rows are 16-byte aligned and W % 16 == 0; 2 = any even W;
+                                      // 0 = same as no_align16
     long opt_batch_loop = 1;          // rectify_batch_kernel (default); 0 = one CTA per (tile, eye, frame)
     long opt_fused_resize = 0;        // 1 = one-launch rectify + resize + normalise (rectify_ws_kernel<..., RESIZE>) where it applies; 0 = three launches
                                       // (measured on 64 pairs 1080p -> 640x480: 0.79 ms fused against 0.75 ms - the fused kernel is issue-bound)
@@ -181,7 +182,7 @@ struct RectifyArgs {
     int force_generic;                 // testing: never take the fast tile path
     int persistent_ctas;               // > 0: persistent pipelined kernel with this many CTAs (a multiple of the SM count)
     int batch_loop;                    // > 0 (= SM count): one CTA per (tile, eye) walks a run of frames (rectify_batch_kernel)
-    int bulk_copy;                     // (unused: the choice arrives as no_align16)
+    int bulk_copy;                     // option bulk: 0 = never the tensor-copy kernel (arrives as no_align16), 1 = where W % 16 == 0, 2 = any even width with 16-byte-aligned rows
     int no_fixed_size;                 // batch kernel: do not use the 640x480 instantiation (tests, tuning)
     int chunk_taper;                   // batch kernel: percent by which the first / last frame chunk is longer / shorter than the average (0 = equal chunks)
     int chunk_tab;                     // 1: chunk c covers frames [chunk_begin[c], chunk_begin[c + 1]) (filled in by launch_rectify_t)

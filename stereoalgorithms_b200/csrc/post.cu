@@ -63,6 +63,7 @@ __global__ void __launch_bounds__(256) heatmap_kernel(const float* __restrict__ 
     const int frame = blockIdx.y;
     const float mn = dec_ordered(minmax[2 * frame]), mx = dec_ordered(~minmax[2 * frame + 1]);
     const float s = (float)(((double)mx - (double)mn) / 255.0);
+    const float rs = 1.0f / s;                                       // inf for a constant frame: every pixel then takes the exact path
     const float* d = disp + (size_t)frame * disp_frame;
     uint8_t* o = out + (size_t)frame * npix * 3;
     float v[kHeatIters][4];
@@ -81,9 +82,20 @@ __global__ void __launch_bounds__(256) heatmap_kernel(const float* __restrict__ 
         uint32_t px[4];
 #pragma unroll
         for (int k = 0; k < 4; k++) {
-            const float n = fabsf(__fdiv_rn(__fsub_rn(v[it][k], mn), s));
-            int idx = __float2int_rn(n);            // NaN -> 0, like saturate_cast<uchar>(cvRound(NaN) = INT_MIN)
-            idx = min(255, max(0, idx));
+            // idx = sat_u8(round_half_even(|fl(x / s)|)), x = fl(d - min).  The IEEE division is a dozen instructions per pixel; the
+            // product with the reciprocal is within 2 ulp of it (< 1e-4 below 512), so wherever that product is at least 1e-4 away
+            // from a half-integer both round to the same integer - and everything >= 255.5 saturates.  The rest (2 pixels in 10^4,
+            // NaN, inf, s = 0) take the division.
+            const float x = __fsub_rn(v[it][k], mn);
+            const float q = fabsf(x * rs);
+            const float t = q + 12582912.0f;          // 1.5 * 2^23: the sum's low mantissa bits are round_half_even(q) for q < 2^22
+            const float r = t - 12582912.0f;
+            int idx;
+            if (q < 512.0f && fabsf(fabsf(q - r) - 0.5f) > 1e-4f) idx = min(255, __float_as_int(t) - 0x4b400000);
+            else {
+                idx = __float2int_rn(fabsf(__fdiv_rn(x, s)));     // NaN -> 0, like saturate_cast<uchar>(cvRound(NaN) = INT_MIN)
+                idx = min(255, max(0, idx));
+            }
             px[k] = s_jet[idx];
         }
         if (VEC) {

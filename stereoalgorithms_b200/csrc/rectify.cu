@@ -1521,7 +1521,10 @@ cudaError_t launch_rectify_t(const RectifyArgs& a, bool aligned4, int tiles_x, i
             // 16-byte-aligned input and footprints that fit a ring stage: the warp-specialised kernel
             // (any even width: what matters is that every ROW starts 16-byte aligned - dense 640 / 1920 / 3840-wide frames, or a
             // padded pitch such as cudaMallocPitch / cv::cuda::GpuMat give a 1242-wide one)
-            const bool a16 = fast_ok_any_w && !a.no_align16 && !a.force_unaligned && a.W % 2 == 0 && a.src_pitch % 16 == 0 && a.src_frame % 16 == 0 &&
+            // Widths that are not a multiple of 16 take it only on request (option bulk = 2): measured on 256 pairs of 1242x375 with
+            // 3728-byte rows it is slower than the batch kernel (1.18 against 0.98 ms; ncu: warps parked on the copies' mbarriers).
+            const bool a16 = fast_ok_any_w && !a.no_align16 && !a.force_unaligned && (a.W % 16 == 0 || (a.W % 2 == 0 && a.bulk_copy >= 2)) && a.src_pitch % 16 == 0 &&
+                             a.src_frame % 16 == 0 &&
                              ((uintptr_t)a.src[0] | (uintptr_t)a.src[1]) % 16 == 0 && a.box_w > 0 && a.box_w % 16 == 0 && a.box_w <= kWsMaxW && a.box_h <= kWsMaxH;
             if (a16) {
                 // box of the tensor copies = the largest footprint of the calibration (a multiple of 16 pixels wide), in 4-byte words

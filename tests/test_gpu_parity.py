@@ -504,9 +504,9 @@ def test_heatmap_after_reproject_uses_fused_minmax(calibs, demo_pair):
 def test_resize_path(calibs, src, dst, model, dtype, fused):
     """a8: rectify at full size -> OpenCV's 8-bit INTER_LINEAR downscale (exact 2x: rounded 2x2 mean) -> tensors; output widths
     that are / are not multiples of 4, pitched rectified rows of odd source widths, a ~10x reduction; both tensor types.
-    fused = 1 (option fused_resize): the one-launch rectify + resize + normalise kernel where it applies (16-byte-aligned rows:
-    1920, 1280 and 4000 wide here - checked by the launch count); fused = 0, the default: rectify, resize and preprocess as
-    three launches everywhere."""
+    fused = 1 (option fused_resize): the one-launch rectify + resize + normalise kernel where it applies (even widths: host frames
+    are uploaded with rows padded to 16 bytes - checked by the launch count); fused = 0, the default: rectify, resize and
+    preprocess as three launches."""
     from stereoalgorithms_b200.geometry import DENSE, F16, F32, MODELS
     W, H = src
     s = W / 640
@@ -518,9 +518,10 @@ def test_resize_path(calibs, src, dst, model, dtype, fused):
     with geom(W, H, model=model, net_size=dst, dtype=F16 if dtype == "f16" else F32, max_batch=2) as g:
         g.set_calibration(c)
         g.set_option("fused_resize", fused)
+        g.set_option("bulk", 2)                               # the tensor-copy kernels for every even width, not only multiples of 16
         k0 = g.launch_count
         g.rectify_preprocess(np.stack([li, ri]), np.stack([ri, li]))
-        assert g.launch_count - k0 == (1 if fused and W % 16 == 0 else 3)
+        assert g.launch_count - k0 == (1 if fused and W % 2 == 0 else 3)
         assert np.array_equal(g.rectified(1, 0)[0], ref["rect_left"])
         assert np.array_equal(g.rectified(2, 1)[1], OC.remap(li, *O.rectify_maps(c, (W, H))[1]))
         nl, nr = g.net_image(2, 0), g.net_image(2, 1)
@@ -703,9 +704,10 @@ def test_rectified_unaligned_widths_batches(calibs, size, l2_prefetch, source):
     """Widths that are not a multiple of 4: rows (and, for odd W*H, frames) start at every byte alignment, so the batch
     kernel's funnel-shifted loads and its run-wise aligned-word stores (head/tail bytes at warp and row ends, partial tiles
     at the right edge) see all four cases; several frames per CTA; tensors of the last frame checked too.
-    source: host frames are uploaded with rows padded to 16 bytes, so even widths take the tensor-copy kernel ("host"; with
-    bulk = 0 the batch kernel: "host_batch_kernel"); packed device frames take the batch kernel ("device_dense"); device frames
-    with a 16-byte-aligned row pitch (cudaMallocPitch style) the tensor-copy kernel again ("device_pitched")."""
+    source: host frames are uploaded with rows padded to 16 bytes, so with bulk = 2 even widths take the tensor-copy kernel
+    ("host"; with bulk = 0 the batch kernel: "host_batch_kernel"); packed device frames take the batch kernel ("device_dense");
+    device frames with a 16-byte-aligned row pitch (cudaMallocPitch style) and bulk = 2 the tensor-copy kernel again
+    ("device_pitched").  (By default widths that are not a multiple of 16 stay on the batch kernel: measured faster.)"""
     W, H = size
     s = W / 640
     c = O.scale_calibration(calibs["calib_a"], s, crop_y=(480 * s - H) / 2)
@@ -717,7 +719,7 @@ def test_rectified_unaligned_widths_batches(calibs, size, l2_prefetch, source):
     with geom(W, H, model="HitNet", max_batch=n) as g:
         g.set_option("l2_prefetch", l2_prefetch)
         g.set_option("batch_ctas", 1)                     # all frames in one CTA
-        g.set_option("bulk", 0 if source == "host_batch_kernel" else 1)
+        g.set_option("bulk", {"host": 2, "host_batch_kernel": 0, "device_dense": 1, "device_pitched": 2}[source])   # 2: tensor-copy kernel for any even width
         g.set_calibration(c)
         if source.startswith("host"):
             g.rectify_preprocess(L, R)
