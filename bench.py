@@ -51,6 +51,8 @@ WORKLOADS = {
 WORKLOADS.update({
     # BASELINE configs[3] (ii): 1080p capture, network at 640x480 (rectify at full size -> 8-bit INTER_LINEAR resize -> tensors)
     "stream_1080p_resize_640x480_b64_f32": dict(model="FastACVNet_plus", W=1920, H=1080, net=(640, 480), batch=64, dtype="f32", calib=("calib_a", 3.0)),
+    "exp_1248x375_b256_f32": dict(model="FastACVNet_plus", W=1248, H=375, batch=256, dtype="f32", calib=("calib_a", 1248 / 640)),
+    "exp_1248x384_b256_f32": dict(model="FastACVNet_plus", W=1248, H=384, batch=256, dtype="f32", calib=("calib_a", 1248 / 640)),
     "exp_1240x375_b256_f32": dict(model="FastACVNet_plus", W=1240, H=375, batch=256, dtype="f32", calib=("calib_a", 1240 / 640)),
     "exp_1242x375_b64_f32": dict(model="FastACVNet_plus", W=1242, H=375, batch=64, dtype="f32", calib=("calib_a", 1242 / 640)),
     "exp_1242x376_b256_f32": dict(model="FastACVNet_plus", W=1242, H=376, batch=256, dtype="f32", calib=("calib_a", 1242 / 640)),
