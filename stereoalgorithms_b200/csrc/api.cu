@@ -299,6 +299,13 @@ static int stage_reproject(sa_handle* h, int f0, int n, int mode, float* dev_out
     a.blk_minmax = h->blk_minmax + 2 * (size_t)f0 * nblk;
     a.blk_counts = h->blk_counts + (size_t)f0 * nblk;
     a.blk_offsets = h->blk_offsets + (size_t)f0 * nblk;
+    if (mode == SA_COMPACT && h->opt_single_pass_compact) {
+        a.status = h->blk_status + (size_t)f0 * nblk;
+        a.ticket = h->blk_status + (size_t)h->max_n * nblk;
+        a.epoch = ++h->cmp_epoch;
+        if (h->cmp_epoch >= (1u << 30)) h->cmp_epoch = 0;  // 30 bits in the word; the wrap needs a clean slate
+        if (h->cmp_epoch == 0) { SA_CUDA(h, cudaMemsetAsync(h->blk_status, 0, ((size_t)h->max_n * nblk + 1) * sizeof(unsigned long long), s)); a.epoch = h->cmp_epoch = 1; }
+    }
     a.counts = dev_counts;
     (void)npix;
     {
@@ -407,6 +414,8 @@ int sa_create(const sa_config* cfg, sa_handle** out)
     A(dev_alloc(&h->minmax, N * 2));
     A(dev_alloc(&h->blk_counts, N * nblk));
     A(dev_alloc(&h->blk_offsets, N * nblk));
+    A(dev_alloc(&h->blk_status, N * nblk + 1));
+    if (ok) A(cudaMemset(h->blk_status, 0, (N * nblk + 1) * sizeof(unsigned long long)));
     A(dev_alloc(&h->blk_minmax, N * nblk * 2));
     A(dev_alloc(&h->lut32, 768));
     A(dev_alloc(&h->lut16, 768));
@@ -471,7 +480,7 @@ int sa_destroy(sa_handle* h)
         cudaFree(h->raw[e]); cudaFree(h->rect[e]); cudaFree(h->net_u8[e]); cudaFree(h->map1[e]); cudaFree(h->map2[e]); cudaFree(h->tiles[e]); cudaFree(h->tmap[e]);
     }
     cudaFree(h->tensor[0]); cudaFree(h->disp); cudaFree(h->points); cudaFree(h->heat); cudaFree(h->counts); cudaFree(h->minmax);
-    cudaFree(h->fp_max); cudaFree(h->blk_counts); cudaFree(h->blk_offsets); cudaFree(h->blk_minmax); cudaFree(h->lut32); cudaFree(h->lut16); cudaFree(h->rs_x); cudaFree(h->rs_y); cudaFree(h->rs_nx); cudaFree(h->rs_ny);
+    cudaFree(h->fp_max); cudaFree(h->blk_counts); cudaFree(h->blk_offsets); cudaFree(h->blk_status); cudaFree(h->blk_minmax); cudaFree(h->lut32); cudaFree(h->lut16); cudaFree(h->rs_x); cudaFree(h->rs_y); cudaFree(h->rs_nx); cudaFree(h->rs_ny);
     for (int s = 0; s < SA_STAGE_COUNT_; s++) {
         for (auto ev : h->timer.begin[s]) cudaEventDestroy(ev);
         for (auto ev : h->timer.end[s]) cudaEventDestroy(ev);
@@ -1092,6 +1101,7 @@ int sa_set_option(sa_handle* h, const char* key, long value)
     else if (!std::strcmp(key, "scalar_preprocess")) h->opt_scalar_preprocess = value;
     else if (!std::strcmp(key, "l2_prefetch")) h->opt_l2_prefetch = value;
     else if (!std::strcmp(key, "frame_base")) h->opt_frame_base = value;
+    else if (!std::strcmp(key, "single_pass_compact")) h->opt_single_pass_compact = value;
     else if (!std::strcmp(key, "no_align16")) h->opt_no_align16 = value;
     else if (!std::strcmp(key, "fused_resize")) h->opt_fused_resize = value;
     else if (!std::strcmp(key, "chunk_taper")) h->opt_chunk_taper = value < 0 ? 0 : (value > 95 ? 95 : value);

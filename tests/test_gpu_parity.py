@@ -373,7 +373,10 @@ def test_reproject_odd_sizes(calibs, size):
         g.rectify_preprocess(img, img, rectify=False)
         g.set_disparity(d)
         pts, _ = g.reproject(2, DENSE)
-        cp, cc = g.reproject(2, COMPACT)
+        cp, cc = g.reproject(2, COMPACT)                   # count -> scan -> compact, three launches (default)
+        g.set_option("single_pass_compact", 1)
+        cp2, cc2 = g.reproject(2, COMPACT)                 # single-pass (decoupled look-back) kernel
+        assert np.array_equal(cc, cc2) and np.array_equal(cp, cp2, equal_nan=True)
         heat = g.heatmap(2)
         for i in range(2):
             want, _ = O.reproject_dense(O.FASTACVNET_PLUS, d[i, 0], img[i], c["Q"])
@@ -383,6 +386,32 @@ def test_reproject_odd_sizes(calibs, size):
             assert_close_points(cp[i, :k], wc, f"{size} compact")
             assert np.array_equal(cp[i, :k, 3:], wc[:, 3:])
             assert np.array_equal(heat[i], O.heatmap(d[i, 0]))
+
+
+def test_compaction_single_pass_long_frames_many_launches(calibs):
+    """The single-pass compaction (option single_pass_compact) on frames of 2025 tiles (1920x1080: look-back windows of 32 tiles, many tiles in flight), a batch
+    that is launched several times in a row (the look-back words are never cleared: only the launch's epoch makes them valid),
+    with sparse and dense validity: counts and order exact against the oracle every time."""
+    from stereoalgorithms_b200.geometry import COMPACT
+    W, H, n = 1920, 1080, 3
+    c = O.scale_calibration(calibs["calib_a"], 3.0)
+    rng = np.random.default_rng(11)
+    img = rng.integers(0, 256, (n, H, W, 3), dtype=np.uint8)
+    with geom(W, H, model="FastACVNet_plus", max_batch=n) as g:
+        g.set_calibration(c)
+        g.set_option("single_pass_compact", 1)
+        g.rectify_preprocess(img, img, rectify=False)
+        for density in (0.5, 0.02, 1.0, 0.0):
+            d = rng.uniform(1, 60, (n, 1, H, W)).astype(np.float32)
+            d[rng.random(d.shape) >= density] = -1.0
+            g.set_disparity(d)
+            cp, cc = g.reproject(n, COMPACT)
+            for i in range(n):
+                wc, k, _ = O.reproject_compact(O.FASTACVNET_PLUS, d[i, 0], img[i], c["Q"])
+                assert cc[i] == k, (density, i)
+                if k:
+                    assert np.array_equal(cp[i, :k, 3:], wc[:, 3:]), (density, i)        # same pixels in the same order
+                    assert_close_points(cp[i, :k:97], wc[::97], f"single-pass compact, density {density}")
 
 
 @pytest.mark.parametrize("size", [(1242, 375), (638, 50), (333, 77), (67, 19), (9, 7)])

@@ -10,12 +10,14 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from stereoalgorithms_b200.compat import FastACVNet_plus as F, Mat, RAFTStereo as Rf  # noqa: E402
 
 GOLDEN = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
-iters = int(sys.argv[1]) if len(sys.argv) > 1 else 200
+iters = int(sys.argv[1]) if len(sys.argv) > 1 and sys.argv[1].isdigit() else 200
 import cv2  # noqa: E402  (only to decode the demo frames)
 
 l0, r0 = cv2.imread(os.path.join(GOLDEN, "left0.png")), cv2.imread(os.path.join(GOLDEN, "right0.png"))
 for name, mod, run in (("FastACVNet_plus", F, "RunFastACVNet_plus_RectifyImage"), ("RAFTStereo", Rf, "RunRAFTStereo")):
     p = mod.Initialize("model.onnx", 0, os.path.join(GOLDEN, "calib_a.yml"))
+    if "--register" in sys.argv:
+        mod.SetHostRegister(p, True)       # opt-in page-locking of the reused pointcloud buffer
     pc = np.empty(640 * 480 * 6, np.float32)
     d = Mat()
     fn = getattr(mod, run)
