@@ -259,11 +259,19 @@ static int stage_rectify(sa_handle* h, int f0, int n, const uint8_t* src_l, cons
         p.W = h->w; p.H = h->h; p.n = n; p.model = h->cfg.model; p.dtype = h->cfg.tensor_dtype;
         p.force_scalar = (int)h->opt_scalar_preprocess;
         StageScope t(h, SA_STAGE_RESIZE, s);
-        // (a fused resize + preprocess kernel - 128 x 8 output pixels per CTA, source rows staged with cp.async - was built
-        // and measured slower on 64 pairs 1080p -> 640x480: 0.54 vs 0.43 ms for these two launches; it was removed)
-        SA_CUDA(h, launch_resize(r, s, &h->launches));
-        SA_CUDA(h, launch_preprocess(p, s, &h->launches));
-        if (f0 == 0) { h->color_src[0] = h->net_u8[0]; h->color_src[1] = h->net_u8[1]; h->color_pitch = (size_t)h->w * 3; h->color_frame = nf; }
+        if (h->opt_separate_preprocess) {
+            SA_CUDA(h, launch_resize(r, s, &h->launches));
+            SA_CUDA(h, launch_preprocess(p, s, &h->launches));
+            if (f0 == 0) { h->color_src[0] = h->net_u8[0]; h->color_src[1] = h->net_u8[1]; h->color_pitch = (size_t)h->w * 3; h->color_frame = nf; }
+        } else {
+            // resize + normalise in one launch: tensors straight from the resized values, the u8 image for the left eye only
+            r.tensor[0] = t_l; r.tensor[1] = t_r; r.tensor_frame = tframe; r.lut = lut;
+            r.dtype = h->cfg.tensor_dtype;
+            r.ident = (h->cfg.model == SA_MODEL_RAFTSTEREO || h->cfg.model == SA_MODEL_CRESTEREO) ? 1 : 0;
+            SA_CUDA(h, launch_resize(r, s, &h->launches));
+            h->net_right_frames = 0;                                   // the right resized image is made on request (sa_copy_net_image)
+            if (f0 == 0) { h->color_src[0] = h->net_u8[0]; h->color_src[1] = nullptr; h->color_pitch = (size_t)h->w * 3; h->color_frame = nf; }
+        }
     } else if (!rectify) {
         PreprocArgs p{};
         p.src[0] = src_l; p.src[1] = src_r; p.tensor[0] = t_l; p.tensor[1] = t_r; p.lut = lut;
@@ -1102,6 +1110,7 @@ int sa_set_option(sa_handle* h, const char* key, long value)
     else if (!std::strcmp(key, "l2_prefetch")) h->opt_l2_prefetch = value;
     else if (!std::strcmp(key, "frame_base")) h->opt_frame_base = value;
     else if (!std::strcmp(key, "single_pass_compact")) h->opt_single_pass_compact = value;
+    else if (!std::strcmp(key, "separate_preprocess")) h->opt_separate_preprocess = value;
     else if (!std::strcmp(key, "no_align16")) h->opt_no_align16 = value;
     else if (!std::strcmp(key, "fused_resize")) h->opt_fused_resize = value;
     else if (!std::strcmp(key, "chunk_taper")) h->opt_chunk_taper = value < 0 ? 0 : (value > 95 ? 95 : value);

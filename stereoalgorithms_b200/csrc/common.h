@@ -122,6 +122,7 @@ struct sa_handle {
     long opt_bulk = 1;                // 1 = rectify_ws_kernel (tensor copies + warp specialisation) when the rows are 16-byte aligned and W % 16 == 0; 2 = any even W;
                                       // 0 = same as no_align16
     long opt_batch_loop = 1;          // rectify_batch_kernel (default); 0 = one CTA per (tile, eye, frame)
+    long opt_separate_preprocess = 0; // resize path: 1 = resize_kernel then preprocess4_kernel (round 1) instead of resize_norm_kernel
     long opt_fused_resize = 0;        // 1 = one-launch rectify + resize + normalise (rectify_ws_kernel<..., RESIZE>) where it applies; 0 = three launches
                                       // (measured on 64 pairs 1080p -> 640x480: 0.79 ms fused against 0.75 ms - the fused kernel is issue-bound)
     long opt_no_align16 = 0;          // 1 = keep the 4-byte-aligned frame loop even where the 16-byte one applies
@@ -227,6 +228,11 @@ struct ResizeArgs {
     size_t src_pitch, src_frame;
     int W, H, w, h, n, area2x;
     int one_eye;             // 1: src[0] / dst[0] only (n frames), not both eyes
+    // optional fused normalisation (resize_norm_kernel): tensors written straight from the resized values, u8 image only for eye 0
+    void* tensor[2];         // null: plain u8 resize of both eyes
+    size_t tensor_frame;     // elements between consecutive frames of one eye
+    const void* lut;         // float[3][256] or __half[3][256]
+    int dtype, ident;
 };
 cudaError_t launch_resize(const ResizeArgs& a, cudaStream_t s, long* launches);
 

@@ -529,13 +529,13 @@ def test_heatmap_after_reproject_uses_fused_minmax(calibs, demo_pair):
 @pytest.mark.parametrize("src,dst", [((1920, 1080), (640, 480)), ((1280, 960), (640, 480)), ((1242, 375), (640, 192)), ((1242, 375), (318, 96)),
                                      ((1918, 1078), (959, 539)), ((4000, 600), (402, 60))])
 @pytest.mark.parametrize("model,dtype", [("FastACVNet_plus", "f32"), ("RAFTStereo", "f16")])
-@pytest.mark.parametrize("fused", [1, 0])
+@pytest.mark.parametrize("fused", [1, 0, -1])
 def test_resize_path(calibs, src, dst, model, dtype, fused):
     """a8: rectify at full size -> OpenCV's 8-bit INTER_LINEAR downscale (exact 2x: rounded 2x2 mean) -> tensors; output widths
     that are / are not multiples of 4, pitched rectified rows of odd source widths, a ~10x reduction; both tensor types.
     fused = 1 (option fused_resize): the one-launch rectify + resize + normalise kernel where it applies (even widths: host frames
-    are uploaded with rows padded to 16 bytes - checked by the launch count); fused = 0, the default: rectify, resize and
-    preprocess as three launches."""
+    are uploaded with rows padded to 16 bytes - checked by the launch count); fused = 0, the default: rectify, then resize +
+    normalise in one launch (resize_norm_kernel); fused = -1 (option separate_preprocess): rectify, resize, preprocess."""
     from stereoalgorithms_b200.geometry import DENSE, F16, F32, MODELS
     W, H = src
     s = W / 640
@@ -546,11 +546,12 @@ def test_resize_path(calibs, src, dst, model, dtype, fused):
     ref = O.run_pair(mid, c, li, ri, -d if model == "RAFTStereo" else d, net_size=dst, dtype=np.float16 if dtype == "f16" else np.float32)
     with geom(W, H, model=model, net_size=dst, dtype=F16 if dtype == "f16" else F32, max_batch=2) as g:
         g.set_calibration(c)
-        g.set_option("fused_resize", fused)
+        g.set_option("fused_resize", 1 if fused == 1 else 0)
+        g.set_option("separate_preprocess", 1 if fused == -1 else 0)
         g.set_option("bulk", 2)                               # the tensor-copy kernels for every even width, not only multiples of 16
         k0 = g.launch_count
         g.rectify_preprocess(np.stack([li, ri]), np.stack([ri, li]))
-        assert g.launch_count - k0 == (1 if fused and W % 2 == 0 else 3)
+        assert g.launch_count - k0 == (1 if fused == 1 and W % 2 == 0 else (3 if fused == -1 else 2))
         assert np.array_equal(g.rectified(1, 0)[0], ref["rect_left"])
         assert np.array_equal(g.rectified(2, 1)[1], OC.remap(li, *O.rectify_maps(c, (W, H))[1]))
         nl, nr = g.net_image(2, 0), g.net_image(2, 1)
