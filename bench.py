@@ -388,6 +388,10 @@ def run_workload(args, wname, wl, rank, world, local, headline, sampler=None):
     from stereoalgorithms_b200.geometry import COMPACT, DENSE, F16, F32, PinnedArray, StereoGeometry
 
     n = wl["batch"]
+    if args.strong and world > 1:                            # fixed total batch, contiguous shard per rank (sa_shard_range's partition)
+        from stereoalgorithms_b200.sharding import shard_range
+        b_, e_ = shard_range(wl["batch"], rank, world)
+        n = max(e_ - b_, 1)
     W, H = wl["W"], wl["H"]
     w, h = net_size(wl)
     npix = w * h
@@ -532,7 +536,8 @@ def run_workload(args, wname, wl, rank, world, local, headline, sampler=None):
         per_launch_bytes = bpp(dom) * n
         achieved = per_launch_bytes / (dom_ms / dom_cnt * 1e-3) / 1e9
         total_key = "total_heatmap" if args.heatmap else "total"
-        kernel_names = {"rectify": "rectify_resize_kernel (fused rectify+resize+preprocess)" if wl.get("net") else "rectify_batch_kernel (fused rectify+preprocess)",
+        kernel_names = {"rectify": "rectify_ws_kernel + resize_norm_kernel (or rectify_ws_kernel<RESIZE> with --opt fused_resize=1)" if wl.get("net")
+                        else "rectify_ws_kernel / rectify_batch_kernel (fused rectify+preprocess)",
                         "reproject": "reproject_compact_kernel (+ count, scan)" if compact else "reproject_dense_kernel"}
         roof = {"bound": "hbm", "kernel": kernel_names[dom],
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src, "traffic": None,
@@ -581,6 +586,7 @@ def main():
     ap.add_argument("--no-extra", action="store_true", help="headline workload only")
     ap.add_argument("--no-ref-kernels", action="store_true", help="skip the reference-kernels-on-B200 row")
     ap.add_argument("--heatmap", action="store_true", help="include stage C in the step")
+    ap.add_argument("--strong", action="store_true", help="strong scaling: the workload's batch is the TOTAL, sharded frame-wise over the ranks (default: per GPU)")
     ap.add_argument("--reproject", default="dense", choices=["dense", "compact"], help="stage B mode (compact = validity filter + compaction, extension a9)")
     ap.add_argument("--pitched-rows", action="store_true", help="device frames whose rows are not a multiple of 16 bytes (1242 wide) with a 16-byte-aligned row pitch, not packed")
     ap.add_argument("--frame-fastest", type=int, default=-1)
@@ -644,7 +650,7 @@ def main():
         notes = {"numa_node_rank0": numa,
                  "network_slot": "synthetic disparity written once before timing (RAFTStereo: its sign alternates per step, same work)"}
         line = {"metric": METRIC, "value": head.pop("value"), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-                "ms_per_step": head.pop("ms_per_step"), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "ms_per_step": head.pop("ms_per_step"), "higher_is_better": True, "scaling": "strong" if args.strong else "weak", "vs_baseline": None,
                 "dtype": head.pop("dtype"), "data": "synthetic", "config": cfg}
         line.update(head)
         line.update({"cpu_baseline": cpu, "clocks": clocks, "notes": notes})

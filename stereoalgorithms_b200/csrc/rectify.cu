@@ -902,7 +902,11 @@ __device__ __forceinline__ void ws_produce(const RectifyArgs& a, const TileInfo 
     const int p = threadIdx.x - kRectThreads;                          // 0..127
     const int cx = 6 * (ti.x0 >> 2), cy = ti.y0;                       // box origin: column in 16-bit elements (x0 is a multiple of 16 pixels = 48 bytes), row
     const uint32_t rowb = (uint32_t)bw * 4u, box_bytes = rowb * (uint32_t)bh;
-    const int nunits = (bw / 12) * bh;                                 // 16-pixel units in the box
+    // 16-pixel units to expand: those of THIS tile's footprint (the copy brings the calibration's largest box; most tiles need fewer
+    // rows and some fewer columns of it - one producer warp in four then has nothing to do).  The fused resize kernel expands the
+    // whole box: its halo pixels tap outside the tile's own footprint.
+    const int ucols = RESIZE ? bw / 12 : min(bw / 12, (ti.w + 15) >> 4), urows = RESIZE ? bh : min(bh, (int)ti.h);
+    const int nunits = ucols * urows;
     if (p == 0) {
 #pragma unroll
         for (int j = 0; j < kWsRawStages; j++)
@@ -918,7 +922,7 @@ __device__ __forceinline__ void ws_produce(const RectifyArgs& a, const TileInfo 
 #pragma unroll
     for (int j = 0; j < 2; j++) {
         const int u = p + j * kWsProducers;
-        const int c = u / bh, r = u - c * bh;                          // column-major: the lanes of a quarter-warp hit different bank groups
+        const int c = u / urows, r = u - c * urows;                    // column-major: the lanes of a quarter-warp hit different bank groups
         uraw[j] = u < nunits ? (uint32_t)r * rowb + 48u * (uint32_t)c : 0xffffffffu;       // 0xffffffff = none
         udst[j] = (uint32_t)(r * kWsStride + 16 * c) * 4u;
     }
