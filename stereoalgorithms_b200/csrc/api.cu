@@ -330,14 +330,17 @@ static int stage_heatmap(sa_handle* h, int f0, int n, uint8_t* dev_out /* frame 
     const float* d = h->disp + (size_t)f0 * disp_frame_floats(h);
     unsigned* mm = h->minmax + 2 * (size_t)f0;
     StageScope t(h, SA_STAGE_HEATMAP, s);
-    if (minmax_state == 1) {
-        const int nblk = reproject_blocks_per_frame(h->w, h->h);
+    const int nblk = reproject_blocks_per_frame(h->w, h->h);
+    const unsigned* partials = nullptr;
+    if (minmax_state == 1 && nblk <= kHeatFoldMaxBlocks) {
+        partials = h->blk_minmax + 2 * (size_t)f0 * nblk;              // folded inside the heat map kernel: one launch, not two
+    } else if (minmax_state == 1) {
         SA_CUDA(h, launch_reduce_minmax(h->blk_minmax + 2 * (size_t)f0 * nblk, nblk, n, mm, s, &h->launches));
     } else if (minmax_state == 0) {
         SA_CUDA(h, cudaMemsetAsync(mm, 0xff, sizeof(unsigned) * 2 * (size_t)n, s));
         SA_CUDA(h, launch_minmax(d, disp_frame_floats(h), npix, n, mm, s, &h->launches));
     }
-    SA_CUDA(h, launch_heatmap(d, disp_frame_floats(h), npix, n, mm, dev_out, s, &h->launches));
+    SA_CUDA(h, launch_heatmap(d, disp_frame_floats(h), npix, n, mm, partials, nblk, dev_out, s, &h->launches));
     return SA_OK;
 }
 

@@ -260,7 +260,9 @@ int reproject_blocks_per_frame(int w, int h);
 cudaError_t launch_reduce_minmax(const unsigned* blk_minmax, int nblk, int n, unsigned* minmax, cudaStream_t s, long* launches);
 
 cudaError_t launch_minmax(const float* disp, size_t disp_frame, int npix, int n, unsigned* minmax, cudaStream_t s, long* launches);
-cudaError_t launch_heatmap(const float* disp, size_t disp_frame, int npix, int n, const unsigned* minmax, uint8_t* out, cudaStream_t s, long* launches);
+constexpr int kHeatFoldMaxBlocks = 1024;   // up to this many stage B partials per frame every heat map CTA folds them itself (640x480: 300)
+cudaError_t launch_heatmap(const float* disp, size_t disp_frame, int npix, int n, unsigned* minmax, const unsigned* blk_minmax, int nblk, uint8_t* out, cudaStream_t s,
+                           long* launches);
 cudaError_t launch_stub(float* disp, size_t disp_frame, int planes, int w, int h, int first_frame, int n, unsigned seed, int negate,
                         cudaStream_t s, long* launches);
 cudaError_t launch_disparity_u8(const float* disp, size_t disp_frame, size_t npix, int n, uint8_t* out, cudaStream_t s, long* launches);

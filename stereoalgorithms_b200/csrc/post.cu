@@ -52,18 +52,19 @@ __global__ void __launch_bounds__(256) minmax_kernel(const float* __restrict__ d
 // issued before the first one is used.
 constexpr int kHeatIters = 4;
 
-template <bool VEC>
-__global__ void __launch_bounds__(256) heatmap_kernel(const float* __restrict__ disp, size_t disp_frame, int npix, const unsigned* __restrict__ minmax,
-                                                      uint8_t* __restrict__ out)
+// FOLD: `minmax` holds the per-CTA partials stage B left behind (nblk pairs per frame) instead of the frame's final pair; every CTA
+// folds them itself while its disparity loads are in flight (a few hundred 8-byte words out of L2), which saves the separate
+// one-CTA-per-frame reduction launch in front of this kernel; the first CTA of a frame also stores the final pair to final_mm.
+template <bool VEC, bool FOLD>
+__global__ void __launch_bounds__(256) heatmap_kernel(const float* __restrict__ disp, size_t disp_frame, int npix, const unsigned* __restrict__ minmax, int nblk,
+                                                      unsigned* __restrict__ final_mm, uint8_t* __restrict__ out)
 {
     __shared__ uint32_t s_jet[256];
-    __shared__ uint32_t s_w[8][96];
+    __shared__ unsigned s_mm[16];
+    __shared__ float s_par[3];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     s_jet[tid] = c_jet[tid];
     const int frame = blockIdx.y;
-    const float mn = dec_ordered(minmax[2 * frame]), mx = dec_ordered(~minmax[2 * frame + 1]);
-    const float s = (float)(((double)mx - (double)mn) / 255.0);
-    const float rs = 1.0f / s;                                       // inf for a constant frame: every pixel then takes the exact path
     const float* d = disp + (size_t)frame * disp_frame;
     uint8_t* o = out + (size_t)frame * npix * 3;
     float v[kHeatIters][4];
@@ -74,46 +75,73 @@ __global__ void __launch_bounds__(256) heatmap_kernel(const float* __restrict__ 
         if (VEC) { if (p0 < npix) { const float4 t = *reinterpret_cast<const float4*>(d + p0); v[it][0] = t.x; v[it][1] = t.y; v[it][2] = t.z; v[it][3] = t.w; } }
         else { for (int k = 0; k < 4; k++) if (p0 + k < npix) v[it][k] = d[p0 + k]; }
     }
-    __syncthreads();
+    // frame constants: warp 0 alone finishes the min/max fold and does the double-precision division (a CTA colours only 4096 pixels:
+    // done by every thread, this preamble was a third of all the instructions the kernel executed), the others pick them up
+    if (FOLD) {
+        const uint2* in = reinterpret_cast<const uint2*>(minmax) + (size_t)frame * nblk;
+        unsigned a = 0xffffffffu, b = 0xffffffffu;
+#pragma unroll 1
+        for (int i = tid; i < nblk; i += 256) { const uint2 t = __ldg(in + i); a = min(a, t.x); b = min(b, t.y); }
+        a = __reduce_min_sync(0xffffffffu, a);
+        b = __reduce_min_sync(0xffffffffu, b);
+        if (lane == 0) { s_mm[2 * warp] = a; s_mm[2 * warp + 1] = b; }
+        __syncthreads();
+    }
+    if (warp == 0) {
+        unsigned emn, emx;                                           // (min, ~max) in the order-preserving encoding
+        if (FOLD) {
+            emn = __reduce_min_sync(0xffffffffu, s_mm[2 * (lane & 7)]);
+            emx = __reduce_min_sync(0xffffffffu, s_mm[2 * (lane & 7) + 1]);
+            if (blockIdx.x == 0 && lane == 0) { final_mm[2 * frame] = emn; final_mm[2 * frame + 1] = emx; }
+        } else {
+            emn = minmax[2 * frame]; emx = minmax[2 * frame + 1];
+        }
+        const float mn0 = dec_ordered(emn), mx0 = dec_ordered(~emx);
+        const float s0 = (float)(((double)mx0 - (double)mn0) / 255.0);
+        if (lane == 0) { s_par[0] = mn0; s_par[1] = s0; s_par[2] = 1.0f / s0; }   // 1/s = inf for a constant frame: every pixel then takes the exact path
+    }
+    __syncthreads();                                                 // (also: the colour table is staged)
+    const float mn = s_par[0], s = s_par[1], rs = s_par[2];
 #pragma unroll
     for (int it = 0; it < kHeatIters; it++) {
         const int chunk = blockIdx.x * kHeatIters + it;
         const int p0 = (chunk * 256 + tid) * 4;
-        uint32_t px[4];
+        // idx = sat_u8(round_half_even(|fl(x / s)|)), x = fl(d - min).  The IEEE division is a dozen instructions per pixel; the product
+        // with the reciprocal is within 2 ulp of it (< 3.1e-5 below 256).  Adding 512 + 1/2 + 2/16384 rounds that product to 1/16384ths
+        // and leaves them in the sum's mantissa: bits 14.. = floor(q + 1/2), bits 0..13 = how far q lies above the half-integer (+2).
+        // Low bits 0..4 = within 2/16384 = 1.2e-4 of a half-integer: only there could the product and the quotient round to different
+        // integers.  Those pixels (5 in 16384), NaN, inf, s = 0 and anything >= 500 take the division; everything else that is
+        // >= 255.5 saturates either way.  One test per thread (four pixels), not per pixel.
+        uint32_t off[4];
+        bool ok = true;
 #pragma unroll
         for (int k = 0; k < 4; k++) {
-            // idx = sat_u8(round_half_even(|fl(x / s)|)), x = fl(d - min).  The IEEE division is a dozen instructions per pixel; the
-            // product with the reciprocal is within 2 ulp of it (< 1e-4 below 512), so wherever that product is at least 1e-4 away
-            // from a half-integer both round to the same integer - and everything >= 255.5 saturates.  The rest (2 pixels in 10^4,
-            // NaN, inf, s = 0) take the division.
             const float x = __fsub_rn(v[it][k], mn);
-            const float q = fabsf(x * rs);
-            const float t = q + 12582912.0f;          // 1.5 * 2^23: the sum's low mantissa bits are round_half_even(q) for q < 2^22
-            const float r = t - 12582912.0f;
-            int idx;
-            if (q < 512.0f && fabsf(fabsf(q - r) - 0.5f) > 1e-4f) idx = min(255, __float_as_int(t) - 0x4b400000);
-            else {
-                idx = __float2int_rn(fabsf(__fdiv_rn(x, s)));     // NaN -> 0, like saturate_cast<uchar>(cvRound(NaN) = INT_MIN)
-                idx = min(255, max(0, idx));
-            }
-            px[k] = s_jet[idx];
+            const float q = fabsf(__fmul_rn(x, rs));
+            const uint32_t b = __float_as_uint(__fadd_rn(q, 512.5001220703125f));
+            ok = ok && (q < 500.0f) && ((b & 16383u) >= 5u);
+            off[k] = min((b >> 12) & 0x7fcu, 1020u);                    // byte offset into the colour table
         }
-        if (VEC) {
-            // 12 bytes per lane -> three coalesced 4-byte stores per lane through a warp-private transpose
-            uint32_t* sw = s_w[warp];
-            sw[lane * 3 + 0] = px[0] | (px[1] << 24);
-            sw[lane * 3 + 1] = (px[1] >> 8) | (px[2] << 16);
-            sw[lane * 3 + 2] = (px[2] >> 16) | (px[3] << 8);
-            __syncwarp();
-            const size_t w0 = (size_t)(chunk * 256 + warp * 32) * 3;   // first word of this warp
-            const size_t nwords = (size_t)npix * 3 / 4;
-            uint32_t* ow = reinterpret_cast<uint32_t*>(o);
+        if (!ok) {
 #pragma unroll
-            for (int m = 0; m < 3; m++) {
-                const size_t wi = w0 + lane + 32 * m;
-                if (wi < nwords) ow[wi] = sw[lane + 32 * m];
+            for (int k = 0; k < 4; k++) {
+                int idx = __float2int_rn(fabsf(__fdiv_rn(__fsub_rn(v[it][k], mn), s)));     // NaN -> 0, like saturate_cast<uchar>(cvRound(NaN) = INT_MIN)
+                off[k] = 4u * (uint32_t)min(255, max(0, idx));
             }
-            __syncwarp();                                               // sw is rewritten by the next chunk
+        }
+        uint32_t px[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++) px[k] = *reinterpret_cast<const uint32_t*>(reinterpret_cast<const char*>(s_jet) + off[k]);
+        if (VEC) {
+            // 12 bytes per lane as three 4-byte stores, 12 bytes apart from lane to lane: the three of them fill every sector they
+            // touch, and L2 merges them before anything goes to DRAM.  (A warp-private transpose through shared memory for unit-stride
+            // stores costs more instructions than it saves L1 passes: this kernel is issue-bound, not L1-bound.)
+            if (p0 < npix) {
+                uint32_t* ow = reinterpret_cast<uint32_t*>(o) + (size_t)(p0 >> 2) * 3;
+                ow[0] = __byte_perm(px[0], px[1], 0x4210);
+                ow[1] = __byte_perm(px[1], px[2], 0x5421);
+                ow[2] = __byte_perm(px[2], px[3], 0x6542);
+            }
         } else {
             for (int k = 0; k < 4; k++)
                 if (p0 + k < npix) {
@@ -274,13 +302,18 @@ cudaError_t launch_minmax(const float* disp, size_t disp_frame, int npix, int n,
     return cudaGetLastError();
 }
 
-cudaError_t launch_heatmap(const float* disp, size_t disp_frame, int npix, int n, const unsigned* minmax, uint8_t* out, cudaStream_t s, long* launches)
+// blk_minmax != nullptr: fold stage B's per-CTA partials (nblk pairs per frame) inside the kernel and leave the result in minmax
+cudaError_t launch_heatmap(const float* disp, size_t disp_frame, int npix, int n, unsigned* minmax, const unsigned* blk_minmax, int nblk, uint8_t* out,
+                           cudaStream_t s, long* launches)
 {
     if (n <= 0) return cudaSuccess;
     const bool vec = (npix % 4 == 0) && (disp_frame % 4 == 0) && (((uintptr_t)disp) % 16 == 0) && (((uintptr_t)out) % 4 == 0);
     dim3 grid((unsigned)((npix + 1024 * kHeatIters - 1) / (1024 * kHeatIters)), (unsigned)n);
-    if (vec) heatmap_kernel<true><<<grid, 256, 0, s>>>(disp, disp_frame, npix, minmax, out);
-    else heatmap_kernel<false><<<grid, 256, 0, s>>>(disp, disp_frame, npix, minmax, out);
+    if (blk_minmax) {
+        if (vec) heatmap_kernel<true, true><<<grid, 256, 0, s>>>(disp, disp_frame, npix, blk_minmax, nblk, minmax, out);
+        else heatmap_kernel<false, true><<<grid, 256, 0, s>>>(disp, disp_frame, npix, blk_minmax, nblk, minmax, out);
+    } else if (vec) heatmap_kernel<true, false><<<grid, 256, 0, s>>>(disp, disp_frame, npix, minmax, 0, nullptr, out);
+    else heatmap_kernel<false, false><<<grid, 256, 0, s>>>(disp, disp_frame, npix, minmax, 0, nullptr, out);
     if (launches) ++*launches;
     return cudaGetLastError();
 }

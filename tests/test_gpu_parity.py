@@ -510,19 +510,27 @@ def test_disparity_u8_golden(golden):
             assert np.array_equal(dev.cpu().numpy(), img), tag
 
 
-def test_heatmap_after_reproject_uses_fused_minmax(calibs, demo_pair):
+@pytest.mark.parametrize("W,H,launches", [(640, 480, 2), (1920, 1080, 3)])
+def test_heatmap_after_reproject_uses_fused_minmax(calibs, W, H, launches):
+    """Stage B leaves per-CTA min/max partials; the heat map kernel folds them itself (up to 1024 per frame: one launch), larger
+    frames get the separate fold launch first.  Either way no second pass over the disparity, and a repeated call reuses the pair."""
     from stereoalgorithms_b200.geometry import DENSE
-    d = np.stack([O.synthetic_disparity(640, 480, 40 + i) * (1 + i) for i in range(3)])
-    with geom(640, 480, model="RAFTStereo", max_batch=3) as g:
-        g.set_calibration(calibs["calib_a"])
-        g.rectify_preprocess(np.stack([demo_pair[0]] * 3), np.stack([demo_pair[1]] * 3))
+    d = np.stack([O.synthetic_disparity(W, H, 40 + i) * (1 + i) for i in range(3)])
+    img = np.stack([O.synthetic_image(W, H, 5 + i) for i in range(3)])
+    calib = calibs["calib_a"] if W == 640 else O.scale_calibration(calibs["calib_a"], W / 640, crop_y=(480 * W / 640 - H) / 2)
+    with geom(W, H, model="RAFTStereo", max_batch=3) as g:
+        g.set_calibration(calib)
+        g.rectify_preprocess(img, img)
         g.set_disparity(-d[:, None])
         before = g.launch_count
         g.reproject(3, DENSE, to_host=False)
         hm = g.heatmap(3)
-        assert g.launch_count - before == 3          # reproject + fold of its min/max partials + heatmap: no second pass over the disparity
+        assert g.launch_count - before == launches
         for i in range(3):
             assert np.array_equal(hm[i], O.heatmap(d[i])), i   # on the flipped (positive) disparity
+        before = g.launch_count
+        hm2 = g.heatmap(3)                                     # the frames' final min/max pairs are current now
+        assert g.launch_count - before == 1 and np.array_equal(hm2, hm)
 
 
 # ---- a8: resize path -------------------------------------------------------------------------------------------------
