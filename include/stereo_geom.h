@@ -148,6 +148,24 @@ SA_API int sa_disparity_u8(sa_handle* h, int n, uint8_t* out, int where, sa_stre
 /* Read-backs (the cudaMemcpy D2H + clone of TRTFastACVNet_plus.cpp:163-168; rectified images are what the
  * reference leaves in the caller's cv::Mat). */
 SA_API int sa_copy_rectified(sa_handle* h, int n, int eye, uint8_t* out, int where, sa_stream stream);
+
+/* Compressed capture frames.  The reference's camera delivers MJPG frames, 2W x H with the left and the
+ * right eye side by side (usb_test.py:7-11: 1280x480); cv2.VideoCapture decodes each on the CPU and the three-argument
+ * RectifyImage overload splits it with two clone()s (FastACVNet_plus_Algorithm.cpp:116-131).  Here the n compressed frames
+ * (host pointers, baseline or progressive JPEG, any chroma subsampling, each exactly 2W x H) are decoded on the GPU by nvJPEG
+ * into the handle's capture buffer - u8 [n][H][2W][3], BGR, allocated on the first call - in stream order, and stage A reads
+ * the two eyes out of it in place (byte offset 3W, row pitch 6W).  nvJPEG is loaded from the CUDA toolkit's libnvjpeg.so.12 on
+ * first use: SA_ERR_IO if it is not installed; SA_ERR_PARSE for a damaged stream, SA_ERR_INVALID_ARG for one of another size.
+ * The Huffman stage of small batches runs on the calling thread, so the call returns when the GPU part is queued, not earlier.
+ * Decoded pixels are nvJPEG's, not libjpeg's (what cv2 uses): measured on 1280x480 frames they lie half a grey level lower on
+ * average (nvJPEG truncates where libjpeg rounds), 1 % of the pixels differ by more than 2 and single pixels at chroma edges of
+ * 4:2:0 streams by up to 10 (tests/test_gpu_jpeg.py).  Everything after the decode is exact as everywhere else. */
+SA_API int sa_decode_capture_jpeg(sa_handle* h, int n, const void* const* jpeg, const size_t* jpeg_bytes, sa_stream stream);
+SA_API uint8_t* sa_capture_buffer(sa_handle* h); /* device; NULL before the first decode */
+/* The first n decoded frames, dense u8 [n][H][2W][3], to host (synchronises) or device memory. */
+SA_API int sa_copy_capture(sa_handle* h, int n, uint8_t* out, int where, sa_stream stream);
+/* sa_decode_capture_jpeg + sa_rectify_preprocess(h, n, capture, capture + 3W, 6W, SA_DEVICE, rectify, stream). */
+SA_API int sa_rectify_preprocess_jpeg(sa_handle* h, int n, const void* const* jpeg, const size_t* jpeg_bytes, int rectify, sa_stream stream);
 SA_API int sa_copy_net_image(sa_handle* h, int n, int eye, uint8_t* out, int where, sa_stream stream); /* resized u8, if resizing */
 SA_API int sa_copy_tensor(sa_handle* h, int n, int eye, void* out, int where, sa_stream stream);
 SA_API int sa_copy_disparity(sa_handle* h, int n, float* out, int where, sa_stream stream); /* plane 0 -> [n][h][w] */

@@ -62,6 +62,10 @@ SIGNATURES = {
     "sa_heatmap": (_i, [_vp, _i, _vp, _i, _vp]),
     "sa_disparity_u8": (_i, [_vp, _i, _vp, _i, _vp]),
     "sa_copy_rectified": (_i, [_vp, _i, _i, _vp, _i, _vp]),
+    "sa_decode_capture_jpeg": (_i, [_vp, _i, C.POINTER(_vp), C.POINTER(_sz), _vp]),
+    "sa_capture_buffer": (_vp, [_vp]),
+    "sa_copy_capture": (_i, [_vp, _i, _vp, _i, _vp]),
+    "sa_rectify_preprocess_jpeg": (_i, [_vp, _i, C.POINTER(_vp), C.POINTER(_sz), _i, _vp]),
     "sa_copy_net_image": (_i, [_vp, _i, _i, _vp, _i, _vp]),
     "sa_copy_tensor": (_i, [_vp, _i, _i, _vp, _i, _vp]),
     "sa_copy_disparity": (_i, [_vp, _i, _vp, _i, _vp]),

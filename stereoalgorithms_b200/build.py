@@ -11,7 +11,7 @@ CSRC = os.path.join(PKG, "csrc")
 OBJ = os.path.join(PKG, "_obj")
 LIB = os.path.join(PKG, "libstereo_geom.so")
 
-SOURCES = ["api.cu", "maps.cu", "rectify.cu", "reproject.cu", "post.cu", "multi.cpp", "calib_yaml.cpp", "stereo_rectify.cpp", "compat.cpp"]
+SOURCES = ["api.cu", "maps.cu", "rectify.cu", "reproject.cu", "post.cu", "multi.cpp", "jpeg.cpp", "calib_yaml.cpp", "stereo_rectify.cpp", "compat.cpp"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC,-fvisibility=hidden",
               "-Xptxas", "-v", "--expt-relaxed-constexpr"]
 

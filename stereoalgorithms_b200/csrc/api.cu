@@ -490,6 +490,8 @@ int sa_destroy(sa_handle* h)
     for (int e = 0; e < 2; e++) {
         cudaFree(h->raw[e]); cudaFree(h->rect[e]); cudaFree(h->net_u8[e]); cudaFree(h->map1[e]); cudaFree(h->map2[e]); cudaFree(h->tiles[e]); cudaFree(h->tmap[e]);
     }
+    jpeg_release(h);
+    cudaFree(h->capture);
     cudaFree(h->tensor[0]); cudaFree(h->disp); cudaFree(h->points); cudaFree(h->heat); cudaFree(h->counts); cudaFree(h->minmax);
     cudaFree(h->fp_max); cudaFree(h->blk_counts); cudaFree(h->blk_offsets); cudaFree(h->blk_status); cudaFree(h->blk_minmax); cudaFree(h->lut32); cudaFree(h->lut16); cudaFree(h->rs_x); cudaFree(h->rs_y); cudaFree(h->rs_nx); cudaFree(h->rs_ny);
     for (int s = 0; s < SA_STAGE_COUNT_; s++) {
@@ -717,6 +719,40 @@ int sa_rectify_preprocess(sa_handle* h, int n, const uint8_t* left, const uint8_
     h->minmax_valid = 0;
     h->partial_valid = 0;
     return stage_rectify(h, 0, n, src[0], src[1], src_pitch, src_pitch * h->H, rectify, s);
+}
+
+// ---- f3: compressed side-by-side capture frames ----------------------------------------------------------------------------
+int sa_decode_capture_jpeg(sa_handle* h, int n, const void* const* jpeg, const size_t* jpeg_bytes, sa_stream stream)
+{
+    SA_ENTER(h);
+    SA_CHECK_N(h, n);
+    if (n == 0) return SA_OK;
+    if (!jpeg || !jpeg_bytes) return fail(h, SA_ERR_INVALID_ARG, "sa_decode_capture_jpeg: null argument");
+    const size_t pitch = (size_t)h->W * 6, frame = pitch * h->H;
+    if (!h->capture) SA_CUDA(h, cudaMalloc(&h->capture, frame * (size_t)h->max_n));
+    return jpeg_decode_batch(h, n, jpeg, jpeg_bytes, h->capture, pitch, frame, 2 * h->W, h->H, pick(h, stream));
+}
+
+uint8_t* sa_capture_buffer(sa_handle* h) { return h ? h->capture : nullptr; }
+
+int sa_copy_capture(sa_handle* h, int n, uint8_t* out, int where, sa_stream stream)
+{
+    SA_ENTER(h);
+    SA_CHECK_N(h, n);
+    if (!out || (where != SA_HOST && where != SA_DEVICE)) return fail(h, SA_ERR_INVALID_ARG, "sa_copy_capture: bad argument");
+    if (!h->capture) return fail(h, SA_ERR_NOT_READY, "sa_copy_capture: no capture frame has been decoded yet");
+    cudaStream_t s = pick(h, stream);
+    SA_CUDA(h, cudaMemcpyAsync(out, h->capture, (size_t)n * h->H * h->W * 6, where == SA_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, s));
+    if (where == SA_HOST) SA_CUDA(h, cudaStreamSynchronize(s));
+    return SA_OK;
+}
+
+int sa_rectify_preprocess_jpeg(sa_handle* h, int n, const void* const* jpeg, const size_t* jpeg_bytes, int rectify, sa_stream stream)
+{
+    const int rc = sa_decode_capture_jpeg(h, n, jpeg, jpeg_bytes, stream);
+    if (rc != SA_OK || n == 0) return rc;
+    // the two eyes are the same buffer 3W bytes apart, rows 6W bytes apart: no split, no copy (the reference clones both halves)
+    return sa_rectify_preprocess(h, n, h->capture, h->capture + (size_t)h->W * 3, (size_t)h->W * 6, SA_DEVICE, rectify, stream);
 }
 
 void* sa_input_tensor(sa_handle* h, int eye) { return h ? h->tensor[(eye == 1 && h->cfg.model != SA_MODEL_HITNET) ? 1 : 0] : nullptr; }

@@ -44,6 +44,10 @@ struct StageTimer {
 
 }  // namespace sa
 
+namespace sa {
+struct JpegDecoder;   // nvJPEG state of one handle (csrc/jpeg.cpp)
+}
+
 struct sa_handle {
     sa_config cfg{};
     int W = 0, H = 0, w = 0, h = 0;  // image / network size
@@ -64,6 +68,8 @@ struct sa_handle {
 
     // device buffers
     uint8_t* raw[2] = {nullptr, nullptr};     // uploaded camera frames   [N][H][W][3]
+    uint8_t* capture = nullptr;               // decoded side-by-side capture frames [N][H][2W][3] (sa_decode_capture_jpeg; allocated on first use)
+    sa::JpegDecoder* jpeg = nullptr;
     uint8_t* rect[2] = {nullptr, nullptr};    // rectified frames         [N][H][W][3]
     uint8_t* net_u8[2] = {nullptr, nullptr};  // resized frames (resize only) [N][h][w][3]
     void* tensor[2] = {nullptr, nullptr};     // network inputs; HitNet: tensor[1] = tensor[0] + 3 planes
@@ -137,6 +143,9 @@ struct sa_handle {
 namespace sa {
 
 int fail(sa_handle* h, int code, const char* fmt, ...);
+// csrc/jpeg.cpp: n JPEG streams of width x height -> BGR frames at dst (device; `pitch` bytes per row, `frame` bytes apart), queued on s
+int jpeg_decode_batch(sa_handle* h, int n, const void* const* jpeg, const size_t* bytes, uint8_t* dst, size_t pitch, size_t frame, int width, int height, cudaStream_t s);
+void jpeg_release(sa_handle* h);
 void set_global_error(const char* msg);
 
 #define SA_CUDA(h, expr)                                                                               \

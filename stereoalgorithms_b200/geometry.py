@@ -144,6 +144,35 @@ class StereoGeometry:
         self._check(self._lib.sa_rectify_preprocess(self._h, n, p, p + 3 * self.W, 6 * self.W, DEVICE if dev else HOST, 1 if rectify else 0, stream))
         return n
 
+    @staticmethod
+    def _jpeg_args(jpegs):
+        bufs = [bytes(j) for j in jpegs]                       # (kept alive by the caller's frame: ctypes only borrows them)
+        ptrs = (C.c_void_p * len(bufs))(*[C.cast(C.c_char_p(b), C.c_void_p) for b in bufs])
+        sizes = (C.c_size_t * len(bufs))(*[len(b) for b in bufs])
+        return bufs, ptrs, sizes
+
+    def decode_capture_jpeg(self, jpegs, stream=None) -> int:
+        """jpegs: n compressed side-by-side capture frames (bytes; 2W x H each) - what the reference's MJPG camera delivers
+        (usb_test.py:7-11) - decoded on the GPU into the handle's capture buffer.  -> n"""
+        bufs, ptrs, sizes = self._jpeg_args(jpegs)
+        self._check(self._lib.sa_decode_capture_jpeg(self._h, len(bufs), ptrs, sizes, stream))
+        return len(bufs)
+
+    def rectify_preprocess_jpeg(self, jpegs, rectify: bool = True, stream=None) -> int:
+        """decode_capture_jpeg + stage A on the two halves of the decoded frames, in place (no split, no copy)."""
+        bufs, ptrs, sizes = self._jpeg_args(jpegs)
+        self._check(self._lib.sa_rectify_preprocess_jpeg(self._h, len(bufs), ptrs, sizes, 1 if rectify else 0, stream))
+        return len(bufs)
+
+    def capture_ptr(self) -> int:
+        return int(self._lib.sa_capture_buffer(self._h) or 0)
+
+    def capture(self, n: int, stream=None) -> np.ndarray:
+        """The first n decoded capture frames, uint8 [n, H, 2W, 3] (host copy; synchronises)."""
+        out = np.empty((n, self.H, 2 * self.W, 3), np.uint8)
+        self._check(self._lib.sa_copy_capture(self._h, n, out.ctypes.data, HOST, stream))
+        return out
+
     def input_tensor_ptr(self, eye: int = LEFT) -> int:
         return int(self._lib.sa_input_tensor(self._h, eye))
 
