@@ -488,6 +488,47 @@ def test_heatmap_golden(golden):
             assert md5(hm[0]) == golden["heatmap"][tag]["md5"], tag
 
 
+@pytest.mark.parametrize("fold", [False, True])
+def test_heatmap_ties_and_near_ties(calibs, fold):
+    """The heat map index is round_half_even(|fl(fl(d - min) / s)|).  The kernel multiplies by 1/s and takes the integer from
+    the mantissa of q + 512.5..., falling back to the IEEE division only within 2/16384 of a half-integer: disparities that
+    land exactly on half-integers (s = 1, 1/2, 2: ties, half of them round DOWN to even), one and a few ulps either side of them,
+    and on arbitrary scales must come out as the reference's arithmetic gives them.  fold: through stage B's min/max partials."""
+    from stereoalgorithms_b200.geometry import DENSE
+    W, H = 640, 480
+    rng = np.random.default_rng(77)
+    frames = []
+    for mn, mx in ((0.0, 255.0), (10.0, 137.5), (-3.0, 507.0), (1.25, 77.0), (-40.0, 3.1), (100.0, 100.0 + 255 * 0.3)):
+        mn32, mx32 = np.float32(mn), np.float32(mx)
+        s = np.float32((float(mx32) - float(mn32)) / 255)
+        k = rng.integers(0, 255, W * H).astype(np.float64) + 0.5
+        d = (np.float64(mn32) + k * np.float64(s)).astype(np.float32)
+        ulps = rng.integers(-3, 4, W * H)
+        for u in range(-3, 4):
+            m = ulps == u
+            t = d[m]
+            for _ in range(abs(u)):
+                t = np.nextafter(t, np.float32(np.inf if u > 0 else -np.inf))
+            d[m] = t
+        d[:1000] = rng.uniform(mn, mx, 1000).astype(np.float32)
+        d = np.clip(d, mn32, mx32)
+        d[0], d[1] = mn32, mx32
+        frames.append(d.reshape(H, W))
+    d = np.stack(frames)
+    n = len(frames)
+    with geom(W, H, model="FastACVNet_plus", max_batch=n) as g:
+        g.set_calibration(calibs["calib_a"])
+        g.set_disparity(d[:, None])
+        if fold:
+            img = np.zeros((n, H, W, 3), np.uint8)
+            g.rectify_preprocess(img, img)
+            g.reproject(n, DENSE, to_host=False)
+        hm = g.heatmap(n)
+    for i in range(n):
+        want = O.heatmap(d[i])
+        assert np.array_equal(hm[i], want), (i, int((hm[i] != want).any(axis=2).sum()))
+
+
 def test_disparity_u8_golden(golden):
     """sa_disparity_u8 = the convertTo(CV_8U) inside cv::imwrite("disparity.jpg", disparity): vectors made by cv2."""
     import torch
