@@ -1024,9 +1024,10 @@ __device__ __forceinline__ void ws_consume(const RectifyArgs& a, const TileInfo 
     const int lane = tid & 31;
     const char* const lut_r = reinterpret_cast<const char*>(s_lut) + 4 * (lane & 3);      // this lane's copy of the tables
 
-    uint32_t st = 0, round = 0, so = 0;
-    for (int f = f0; f < f1; f++) {
-        mbar_wait(&s_full[st], round & 1u);
+    // one frame out of BGRx stage `stg` (at byte offset `so` from stage 0); the frame loop below names the two stages explicitly,
+    // so that the stage index, its offset and the barrier addresses are loop constants instead of per-frame arithmetic
+    auto one_frame = [&](const uint32_t so, const int stg, const uint32_t parity) {
+        mbar_wait(&s_full[stg], parity);
 #pragma unroll
         for (int k = 0; k < 4; k++) {
             uint32_t p00, p01, p10, p11;
@@ -1071,11 +1072,16 @@ __device__ __forceinline__ void ws_consume(const RectifyArgs& a, const TileInfo 
             }
         }
         __syncwarp();
-        if (lane == 0) mbar_arrive(&s_empty[st]);                       // this warp has read everything it needs from the stage
+        if (lane == 0) mbar_arrive(&s_empty[stg]);                      // this warp has read everything it needs from the stage
         rp += rect_frame_words;
         if (WRITE_TENSOR) tp += a.tensor_frame;
-        so += stage_b;
-        if (++st == kWsStages) { st = 0; so = 0; ++round; }
+    };
+    static_assert(kWsStages == 2, "the frame loop alternates between two stages");
+    uint32_t parity = 0;
+    for (int f = f0; f < f1; f += 2) {
+        one_frame(0u, 0, parity);
+        if (f + 1 < f1) one_frame(stage_b, 1, parity);
+        parity ^= 1u;
     }
 }
 
