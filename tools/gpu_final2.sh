@@ -17,3 +17,6 @@ CMD2="python bench.py --steps 3 --warmup 3 --no-e2e --no-cpu-baseline --no-ref-k
 $CMD2 > gpurun_out/r02f_plain.json 2> gpurun_out/r02f_plain.err && \
 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -c 60 --csv --log-file gpurun_out/r02_launches_fused_resize.csv $CMD2 > gpurun_out/r02f_ncu1.log 2>&1
 echo "fused launch list rc=$?"
+bash tools/gpu_r2i.sh | tail -8
+python tools/jpeg_capture_bench.py --n 64 > gpurun_out/jpeg64.json 2> gpurun_out/jpeg64.err; echo "jpeg rc=$?"; cut -c1-300 gpurun_out/jpeg64.json
+bash tools/gpu_prof3.sh r02heat heatmap_kernel --no-extra --heatmap
