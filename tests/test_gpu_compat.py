@@ -231,3 +231,57 @@ def test_engine_on_the_reference_named_path_is_ordered_on_the_handle_stream(demo
     assert F.SetEngine(p, None) == 0
     assert F.RunFastACVNet_plus_RectifyImage(p, imageL.copy(), imageR.copy(), pointcloud, disparity) == 0
     assert F.Release(p) == 0
+
+
+def test_device_resident_step_can_be_captured_in_a_cuda_graph_and_replayed(calibs):
+    """Stage A -> (network slot: here the stub) -> stage B -> stage C on device buffers, on a caller's stream, neither allocate nor
+    synchronise nor record events (unless SA_FLAG_TIMING asks for them): the whole step can be captured once in a CUDA graph and
+    replayed on new frames in the same buffers - the way a serving loop removes the per-launch cost of a batch-1 step.
+    (The tensor-copy descriptors of the warp-specialised stage A kernel are kernel parameters: captured by value.)"""
+    import torch
+    from oracle import oracle as O
+    from oracle import oracle_c as OC
+    from stereoalgorithms_b200.geometry import DENSE, StereoGeometry
+    from test_gpu_parity import assert_close_points
+    W, H, n = 640, 480, 3
+    c = calibs["calib_a"]
+    rng = np.random.default_rng(3)
+    frames = [rng.integers(0, 256, (2, n, H, W, 3), dtype=np.uint8) for _ in range(2)]
+    dL = torch.empty((n, H, W, 3), dtype=torch.uint8, device="cuda")
+    dR = torch.empty_like(dL)
+    pts = torch.zeros((n, W * H, 6), dtype=torch.float32, device="cuda")
+    heat = torch.zeros((n, H, W, 3), dtype=torch.uint8, device="cuda")
+    (l1, l2), (r1, r2) = O.rectify_maps(c, (W, H))
+    with StereoGeometry(W, H, model="FastACVNet_plus", max_batch=n) as g:
+        g.set_calibration(c)
+        s = torch.cuda.Stream()
+        sp = s.cuda_stream
+
+        def step():
+            g.rectify_preprocess(dL, dR, n=n, stream=sp)
+            g.stub_disparity(n, seed=11, stream=sp)
+            g.reproject(n, DENSE, out=pts, to_host=False, stream=sp)
+            g.heatmap(n, out=heat, to_host=False, stream=sp)
+
+        dL.copy_(torch.from_numpy(frames[0][0])); dR.copy_(torch.from_numpy(frames[0][1]))
+        torch.cuda.synchronize()
+        with torch.cuda.stream(s):
+            step()                                             # warm-up outside the capture (lazy one-time set-up)
+        s.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=s):
+            step()
+        for k in (1, 0):
+            dL.copy_(torch.from_numpy(frames[k][0])); dR.copy_(torch.from_numpy(frames[k][1]))
+            pts.zero_(); heat.zero_()
+            torch.cuda.synchronize()
+            graph.replay()
+            torch.cuda.synchronize()
+            disp = g.disparity(n)
+            got, hm = pts.cpu().numpy(), heat.cpu().numpy()
+            for i in range(n):
+                wl = OC.remap(frames[k][0][i], l1, l2)
+                assert np.array_equal(g.rectified(n, 0)[i], wl) and np.array_equal(g.rectified(n, 1)[i], OC.remap(frames[k][1][i], r1, r2)), (k, i)
+                want, _ = O.reproject_dense(O.FASTACVNET_PLUS, disp[i], wl, c["Q"])
+                assert_close_points(got[i], want, f"graph replay {k}, frame {i}")
+                assert np.array_equal(hm[i], O.heatmap(disp[i])), (k, i)
