@@ -54,6 +54,8 @@ WORKLOADS.update({
     "exp_1248x375_b256_f32": dict(model="FastACVNet_plus", W=1248, H=375, batch=256, dtype="f32", calib=("calib_a", 1248 / 640)),
     "exp_1248x384_b256_f32": dict(model="FastACVNet_plus", W=1248, H=384, batch=256, dtype="f32", calib=("calib_a", 1248 / 640)),
     "exp_1240x375_b256_f32": dict(model="FastACVNet_plus", W=1240, H=375, batch=256, dtype="f32", calib=("calib_a", 1240 / 640)),
+    "exp_1244x375_b256_f32": dict(model="FastACVNet_plus", W=1244, H=375, batch=256, dtype="f32", calib=("calib_a", 1244 / 640)),
+    "exp_1242x375_b256_f16": dict(model="FastACVNet_plus", W=1242, H=375, batch=256, dtype="f16", calib=("calib_a", 1242 / 640)),
     "exp_1242x375_b64_f32": dict(model="FastACVNet_plus", W=1242, H=375, batch=64, dtype="f32", calib=("calib_a", 1242 / 640)),
     "exp_1242x376_b256_f32": dict(model="FastACVNet_plus", W=1242, H=376, batch=256, dtype="f32", calib=("calib_a", 1242 / 640)),
 })
