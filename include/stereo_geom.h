@@ -166,6 +166,19 @@ SA_API uint8_t* sa_capture_buffer(sa_handle* h); /* device; NULL before the firs
 SA_API int sa_copy_capture(sa_handle* h, int n, uint8_t* out, int where, sa_stream stream);
 /* sa_decode_capture_jpeg + sa_rectify_preprocess(h, n, capture, capture + 3W, 6W, SA_DEVICE, rectify, stream). */
 SA_API int sa_rectify_preprocess_jpeg(sa_handle* h, int n, const void* const* jpeg, const size_t* jpeg_bytes, int rectify, sa_stream stream);
+
+/* JPEG files of the 8-bit outputs.  The demos store the disparity and the heat map with
+ * cv::imwrite("disparity.jpg", ...) / cv::imwrite("heatmap.jpg", ...) (FastACVNet_plus/test/main.cpp:55,59): baseline JPEG,
+ * quality 95, colour 4:2:0.  sa_encode_jpeg does that on the GPU (nvJPEG, same run-time dependency as above) for one image -
+ * channels = 1 (grey: sa_disparity_u8's output) or 3 (BGR interleaved: sa_heatmap's, sa_copy_rectified's), host or device memory,
+ * `pitch` bytes per row (0 = dense).  The stream is returned in `out` (host; out = NULL: only *out_bytes, the size needed) -
+ * nvJPEG's bytes, not libjpeg's: same format and quality setting, not the same file.  Synchronises the stream.
+ * sa_write_jpeg = encode + fwrite.  sa_decode_jpeg is the counterpart for ONE image of any size (BGR interleaved out, host or
+ * device; out = NULL: only the size), e.g. to read a stored frame back. */
+SA_API int sa_encode_jpeg(sa_handle* h, const uint8_t* image, int where, int width, int height, int channels, size_t pitch, int quality, void* out,
+                          size_t out_capacity, size_t* out_bytes, sa_stream stream);
+SA_API int sa_write_jpeg(sa_handle* h, const char* path, const uint8_t* image, int where, int width, int height, int channels, size_t pitch, int quality);
+SA_API int sa_decode_jpeg(sa_handle* h, const void* jpeg, size_t jpeg_bytes, uint8_t* out, int where, size_t pitch, int* width, int* height, sa_stream stream);
 SA_API int sa_copy_net_image(sa_handle* h, int n, int eye, uint8_t* out, int where, sa_stream stream); /* resized u8, if resizing */
 SA_API int sa_copy_tensor(sa_handle* h, int n, int eye, void* out, int where, sa_stream stream);
 SA_API int sa_copy_disparity(sa_handle* h, int n, float* out, int where, sa_stream stream); /* plane 0 -> [n][h][w] */

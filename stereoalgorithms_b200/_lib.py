@@ -66,6 +66,9 @@ SIGNATURES = {
     "sa_capture_buffer": (_vp, [_vp]),
     "sa_copy_capture": (_i, [_vp, _i, _vp, _i, _vp]),
     "sa_rectify_preprocess_jpeg": (_i, [_vp, _i, C.POINTER(_vp), C.POINTER(_sz), _i, _vp]),
+    "sa_encode_jpeg": (_i, [_vp, _vp, _i, _i, _i, _i, _sz, _i, _vp, _sz, C.POINTER(_sz), _vp]),
+    "sa_write_jpeg": (_i, [_vp, _cp, _vp, _i, _i, _i, _i, _sz, _i]),
+    "sa_decode_jpeg": (_i, [_vp, _vp, _sz, _vp, _i, _sz, C.POINTER(_i), C.POINTER(_i), _vp]),
     "sa_copy_net_image": (_i, [_vp, _i, _i, _vp, _i, _vp]),
     "sa_copy_tensor": (_i, [_vp, _i, _i, _vp, _i, _vp]),
     "sa_copy_disparity": (_i, [_vp, _i, _vp, _i, _vp]),

@@ -492,6 +492,7 @@ int sa_destroy(sa_handle* h)
     }
     jpeg_release(h);
     cudaFree(h->capture);
+    cudaFree(h->jpeg_scratch);
     cudaFree(h->tensor[0]); cudaFree(h->disp); cudaFree(h->points); cudaFree(h->heat); cudaFree(h->counts); cudaFree(h->minmax);
     cudaFree(h->fp_max); cudaFree(h->blk_counts); cudaFree(h->blk_offsets); cudaFree(h->blk_status); cudaFree(h->blk_minmax); cudaFree(h->lut32); cudaFree(h->lut16); cudaFree(h->rs_x); cudaFree(h->rs_y); cudaFree(h->rs_nx); cudaFree(h->rs_ny);
     for (int s = 0; s < SA_STAGE_COUNT_; s++) {
@@ -753,6 +754,84 @@ int sa_rectify_preprocess_jpeg(sa_handle* h, int n, const void* const* jpeg, con
     if (rc != SA_OK || n == 0) return rc;
     // the two eyes are the same buffer 3W bytes apart, rows 6W bytes apart: no split, no copy (the reference clones both halves)
     return sa_rectify_preprocess(h, n, h->capture, h->capture + (size_t)h->W * 3, (size_t)h->W * 6, SA_DEVICE, rectify, stream);
+}
+
+// ---- f4: JPEG files of the demos' 8-bit outputs -------------------------------------------------------------------------------
+static int jpeg_scratch(sa_handle* h, size_t bytes)
+{
+    if (h->jpeg_scratch_bytes >= bytes) return SA_OK;
+    cudaFree(h->jpeg_scratch);
+    h->jpeg_scratch = nullptr;
+    h->jpeg_scratch_bytes = 0;
+    SA_CUDA(h, cudaMalloc(&h->jpeg_scratch, bytes));
+    h->jpeg_scratch_bytes = bytes;
+    return SA_OK;
+}
+
+int sa_encode_jpeg(sa_handle* h, const uint8_t* image, int where, int width, int height, int channels, size_t pitch, int quality, void* out, size_t out_capacity,
+                   size_t* out_bytes, sa_stream stream)
+{
+    SA_ENTER(h);
+    if (!image || !out_bytes || width <= 0 || height <= 0 || (channels != 1 && channels != 3) || (where != SA_HOST && where != SA_DEVICE))
+        return fail(h, SA_ERR_INVALID_ARG, "sa_encode_jpeg: bad argument");
+    if (width > 65535 || height > 65535) return fail(h, SA_ERR_TOO_LARGE, "sa_encode_jpeg: %dx%d exceeds JPEG's 65535 x 65535", width, height);
+    const size_t row = (size_t)width * channels;
+    if (pitch == 0) pitch = row;
+    if (pitch < row) return fail(h, SA_ERR_INVALID_ARG, "sa_encode_jpeg: pitch %zu < row bytes %zu", pitch, row);
+    if (quality < 1 || quality > 100) return fail(h, SA_ERR_INVALID_ARG, "sa_encode_jpeg: quality %d outside 1..100", quality);
+    cudaStream_t s = pick(h, stream);
+    const uint8_t* dev = image;
+    if (where == SA_HOST) {
+        if (const int rc = jpeg_scratch(h, row * height)) return rc;
+        SA_CUDA(h, cudaMemcpy2DAsync(h->jpeg_scratch, row, image, pitch, row, (size_t)height, cudaMemcpyHostToDevice, s));
+        dev = h->jpeg_scratch;
+        pitch = row;
+    }
+    std::vector<unsigned char> bytes;
+    if (const int rc = jpeg_encode(h, dev, width, height, channels, pitch, quality, bytes, s)) return rc;
+    *out_bytes = bytes.size();
+    if (!out) return SA_OK;                                            // size query
+    if (out_capacity < bytes.size()) return fail(h, SA_ERR_TOO_LARGE, "sa_encode_jpeg: the stream has %zu bytes, the buffer %zu", bytes.size(), out_capacity);
+    std::memcpy(out, bytes.data(), bytes.size());
+    return SA_OK;
+}
+
+int sa_write_jpeg(sa_handle* h, const char* path, const uint8_t* image, int where, int width, int height, int channels, size_t pitch, int quality)
+{
+    SA_ENTER(h);
+    if (!path) return fail(h, SA_ERR_INVALID_ARG, "sa_write_jpeg: null path");
+    size_t n = 0;
+    if (const int rc = sa_encode_jpeg(h, image, where, width, height, channels, pitch, quality, nullptr, 0, &n, nullptr)) return rc;
+    std::vector<unsigned char> buf(n);
+    if (const int rc = sa_encode_jpeg(h, image, where, width, height, channels, pitch, quality, buf.data(), buf.size(), &n, nullptr)) return rc;
+    FILE* f = std::fopen(path, "wb");
+    if (!f) return fail(h, SA_ERR_IO, "sa_write_jpeg: cannot open %s", path);
+    const bool ok = std::fwrite(buf.data(), 1, n, f) == n;
+    if (std::fclose(f) != 0 || !ok) return fail(h, SA_ERR_IO, "sa_write_jpeg: short write to %s", path);
+    return SA_OK;
+}
+
+int sa_decode_jpeg(sa_handle* h, const void* jpeg, size_t jpeg_bytes, uint8_t* out, int where, size_t pitch, int* width, int* height, sa_stream stream)
+{
+    SA_ENTER(h);
+    if (!jpeg || jpeg_bytes == 0 || !width || !height || (where != SA_HOST && where != SA_DEVICE)) return fail(h, SA_ERR_INVALID_ARG, "sa_decode_jpeg: bad argument");
+    int w = 0, hh = 0;
+    if (const int rc = jpeg_image_size(h, jpeg, jpeg_bytes, &w, &hh)) return rc;
+    *width = w;
+    *height = hh;
+    if (!out) return SA_OK;                                            // size query
+    const size_t row = (size_t)w * 3;
+    if (pitch == 0) pitch = row;
+    if (pitch < row) return fail(h, SA_ERR_INVALID_ARG, "sa_decode_jpeg: pitch %zu < 3*width = %zu", pitch, row);
+    cudaStream_t s = pick(h, stream);
+    const void* one[1] = {jpeg};
+    const size_t len[1] = {jpeg_bytes};
+    if (where == SA_DEVICE) return jpeg_decode_checked(h, 1, one, len, out, pitch, 0, s);
+    if (const int rc = jpeg_scratch(h, row * hh)) return rc;
+    if (const int rc = jpeg_decode_checked(h, 1, one, len, h->jpeg_scratch, row, 0, s)) return rc;
+    SA_CUDA(h, cudaMemcpy2DAsync(out, pitch, h->jpeg_scratch, row, row, (size_t)hh, cudaMemcpyDeviceToHost, s));
+    SA_CUDA(h, cudaStreamSynchronize(s));
+    return SA_OK;
 }
 
 void* sa_input_tensor(sa_handle* h, int eye) { return h ? h->tensor[(eye == 1 && h->cfg.model != SA_MODEL_HITNET) ? 1 : 0] : nullptr; }

@@ -70,6 +70,8 @@ struct sa_handle {
     uint8_t* raw[2] = {nullptr, nullptr};     // uploaded camera frames   [N][H][W][3]
     uint8_t* capture = nullptr;               // decoded side-by-side capture frames [N][H][2W][3] (sa_decode_capture_jpeg; allocated on first use)
     sa::JpegDecoder* jpeg = nullptr;
+    uint8_t* jpeg_scratch = nullptr;          // device staging for sa_encode_jpeg of host images / sa_decode_jpeg to host memory (grown on demand)
+    size_t jpeg_scratch_bytes = 0;
     uint8_t* rect[2] = {nullptr, nullptr};    // rectified frames         [N][H][W][3]
     uint8_t* net_u8[2] = {nullptr, nullptr};  // resized frames (resize only) [N][h][w][3]
     void* tensor[2] = {nullptr, nullptr};     // network inputs; HitNet: tensor[1] = tensor[0] + 3 planes
@@ -146,6 +148,10 @@ int fail(sa_handle* h, int code, const char* fmt, ...);
 // csrc/jpeg.cpp: n JPEG streams of width x height -> BGR frames at dst (device; `pitch` bytes per row, `frame` bytes apart), queued on s
 int jpeg_decode_batch(sa_handle* h, int n, const void* const* jpeg, const size_t* bytes, uint8_t* dst, size_t pitch, size_t frame, int width, int height, cudaStream_t s);
 void jpeg_release(sa_handle* h);
+int jpeg_image_size(sa_handle* h, const void* jpeg, size_t bytes, int* width, int* height);
+int jpeg_decode_checked(sa_handle* h, int n, const void* const* jpeg, const size_t* bytes, uint8_t* dst, size_t pitch, size_t frame, cudaStream_t s);
+// one 8-bit device image (1 channel grey / 3 channels BGR interleaved) -> baseline JPEG bytes; synchronises s
+int jpeg_encode(sa_handle* h, const uint8_t* dev_image, int width, int height, int channels, size_t pitch, int quality, std::vector<unsigned char>& out, cudaStream_t s);
 void set_global_error(const char* msg);
 
 #define SA_CUDA(h, expr)                                                                               \

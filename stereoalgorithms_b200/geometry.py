@@ -164,6 +164,33 @@ class StereoGeometry:
         self._check(self._lib.sa_rectify_preprocess_jpeg(self._h, len(bufs), ptrs, sizes, 1 if rectify else 0, stream))
         return len(bufs)
 
+    def encode_jpeg(self, image, quality: int = 95, stream=None) -> bytes:
+        """image: uint8 [H, W] (grey) or [H, W, 3] (BGR), numpy or a CUDA tensor -> the bytes of a baseline JPEG (what the demos'
+        cv::imwrite("disparity.jpg" / "heatmap.jpg") store, FastACVNet_plus/test/main.cpp:55,59; encoded on the GPU)."""
+        p, dev = _ptr(image)
+        hh, ww = int(image.shape[0]), int(image.shape[1])
+        ch = 1 if len(image.shape) == 2 else int(image.shape[2])
+        need = C.c_size_t(0)
+        where = DEVICE if dev else HOST
+        self._check(self._lib.sa_encode_jpeg(self._h, p, where, ww, hh, ch, 0, quality, None, 0, C.byref(need), stream))
+        buf = (C.c_ubyte * need.value)()
+        self._check(self._lib.sa_encode_jpeg(self._h, p, where, ww, hh, ch, 0, quality, buf, need.value, C.byref(need), stream))
+        return bytes(buf[: need.value])
+
+    def write_jpeg(self, path: str, image, quality: int = 95):
+        p, dev = _ptr(image)
+        ch = 1 if len(image.shape) == 2 else int(image.shape[2])
+        self._check(self._lib.sa_write_jpeg(self._h, path.encode(), p, DEVICE if dev else HOST, int(image.shape[1]), int(image.shape[0]), ch, 0, quality))
+
+    def decode_jpeg(self, data: bytes) -> np.ndarray:
+        """One JPEG stream of any size -> uint8 [H, W, 3] BGR (decoded on the GPU)."""
+        b = bytes(data)
+        w, hh = C.c_int(0), C.c_int(0)
+        self._check(self._lib.sa_decode_jpeg(self._h, b, len(b), None, HOST, 0, C.byref(w), C.byref(hh), None))
+        out = np.empty((hh.value, w.value, 3), np.uint8)
+        self._check(self._lib.sa_decode_jpeg(self._h, b, len(b), out.ctypes.data, HOST, 0, C.byref(w), C.byref(hh), None))
+        return out
+
     def capture_ptr(self) -> int:
         return int(self._lib.sa_capture_buffer(self._h) or 0)
 

@@ -91,3 +91,45 @@ def test_jpeg_capture_errors_are_reported(calibs):
         g.set_calibration(O.scale_calibration(calibs["calib_a"], 0.5))
         with pytest.raises(StereoGeomError, match="1280x480.*640x240"):
             g.decode_capture_jpeg([good])
+
+
+def psnr(a, b):
+    mse = np.mean((a.astype(np.float64) - b.astype(np.float64)) ** 2)
+    return 99.0 if mse == 0 else 10 * np.log10(255.0 ** 2 / mse)
+
+
+def test_demo_outputs_as_jpeg_files_round_trip(tmp_path):
+    """SURVEY.md section 8 f4: the demos store the 8-bit disparity and the heat map with cv::imwrite(".jpg") (FastACVNet_plus/test/
+    main.cpp:55,59).  sa_encode_jpeg / sa_write_jpeg do that on the GPU; the stream must be a JPEG of the right size that decodes
+    back (sa_decode_jpeg, and cv2 where it is installed) to the image within what quality 95 loses, host and device inputs must give
+    the same bytes, and a lower quality a smaller stream."""
+    import torch
+    d = O.synthetic_disparity(640, 480, 3, invalid=False)
+    with geom(640, 480, model="HitNet") as g:
+        g.set_disparity(d[None, None])
+        heat = g.heatmap(1)[0]
+        grey = g.disparity_u8(1)[0]
+        for name, img in (("heatmap", heat), ("disparity", grey)):
+            data = g.encode_jpeg(img, 95)
+            assert data[:2] == b"\xff\xd8" and data[-2:] == b"\xff\xd9", name
+            assert g.encode_jpeg(torch.from_numpy(img).cuda(), 95) == data, name
+            back = g.decode_jpeg(data)
+            want = img if img.ndim == 3 else np.repeat(img[..., None], 3, axis=2)
+            assert back.shape == want.shape, name
+            assert psnr(back, want) > 33.0, (name, psnr(back, want))
+            try:
+                import cv2
+            except ImportError:
+                cv2 = None
+            if cv2 is not None:
+                theirs = cv2.imdecode(np.frombuffer(data, np.uint8), cv2.IMREAD_COLOR if img.ndim == 3 else cv2.IMREAD_GRAYSCALE)
+                assert theirs.shape == img.shape and psnr(theirs, img) > 33.0, (name, psnr(theirs, img))
+        assert len(g.encode_jpeg(heat, 50)) < len(g.encode_jpeg(heat, 95))
+        path = tmp_path / "heatmap.jpg"
+        g.write_jpeg(str(path), heat)
+        assert path.read_bytes() == g.encode_jpeg(heat, 95)
+        from stereoalgorithms_b200.geometry import StereoGeomError
+        with pytest.raises(StereoGeomError, match="quality"):
+            g.encode_jpeg(heat, 0)
+        with pytest.raises(StereoGeomError):
+            g.decode_jpeg(b"\xff\xd8 not a stream")
