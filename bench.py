@@ -135,12 +135,16 @@ class ClockSampler:
         for line in self.proc.stdout:
             self.samples.append((time.time(), line.strip()))
 
-    def stop(self, t0, t1):
+    def stop(self):
+        if self.proc:
+            time.sleep(0.12)
+            self.proc.terminate()
+
+    def window(self, t0, t1):
+        """Clocks and throttle reasons of the samples taken in [t0, t1] (one workload: its warm-up, timed steps and end-to-end leg)."""
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.12)
-        self.proc.terminate()
-        rows = [s for (t, s) in self.samples if t0 <= t <= t1] or [s for (_, s) in self.samples]
+        rows = [s for (t, s) in list(self.samples) if t0 <= t <= t1 + 0.06] or [s for (_, s) in list(self.samples)]
         sm, mx, reasons, power = [], [], set(), []
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for r in rows:
@@ -442,6 +446,7 @@ def run_workload(args, wname, wl, rank, world, local, headline, sampler=None):
             dist.barrier()
         torch.cuda.synchronize()
 
+    t_workload0 = time.time()
     for _ in range(args.warmup):
         step()
     barrier()
@@ -558,7 +563,7 @@ def run_workload(args, wname, wl, rank, world, local, headline, sampler=None):
         res = {"value": value, "unit": UNIT, "ms_per_step": 1e3 * step_time / args.steps, "kernel_ms_per_step": 1e3 * dev_s / args.steps,
                "host_ms_per_step": 1e3 * elapsed / args.steps, "gpu_launches": launches, "roofline": roof, "e2e": e2e,
                "config": dict(workload_config(wname, wl, world, args.reproject, args.heatmap), **({"device_row_pitch": in_pitch} if in_pitch else {})),
-               "_wall": (t_wall0, t_wall1),
+               "_wall": (t_workload0, time.time()),
                "dtype": "u8 fixed-point + f32 (%s tensors)" % wl["dtype"]}
         if compact:
             res["points_kept_per_frame"] = kept
@@ -627,12 +632,13 @@ def main():
     for name in extras:
         r, _ = run_workload(args, name, dict(WORKLOADS[name]), rank, world, local, headline=False)
         if r is not None:
-            r.pop("_wall", None)
+            r["clocks"] = sampler.window(*r.pop("_wall")) if sampler else None
             others[name] = r
 
     if rank == 0:
-        t_wall0, t_wall1 = head.pop("_wall")
-        clocks = sampler.stop(t_wall0, time.time()) if sampler else None
+        clocks = sampler.window(*head.pop("_wall")) if sampler else None      # the headline workload's own window, not the extras'
+        if sampler:
+            sampler.stop()
         n, W, H = wl["batch"], wl["W"], wl["H"]
         w, h = net_size(wl)
         cpu = None
